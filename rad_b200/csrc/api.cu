@@ -1,0 +1,1329 @@
+// api.cu -- the C ABI of include/rad_b200.h: device state, batched build orchestration, search, stateless kernels.
+//
+// Host orchestration replaces usearch/python/lib.cpp:177-268 (add_typed_to_index / add_many_to_index: the
+// executor-driven per-vector loop) and lib.cpp:357-415, 511-557 (search_typed / search_many_in_index).  Instead of a
+// thread pool with per-node locks, an rb_add is ONE stream of kernel launches whose shape (levels, batch boundaries,
+// entry point and max level per batch) is known on the host before the first launch, so there is no device->host
+// synchronisation inside a build.
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cuda_runtime.h>
+
+#include "../../include/rad_b200.h"
+#include "exact_kernels.cuh"
+#include "hnsw_kernels.cuh"
+#include "host_index.hpp"
+#include "synth_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_error;
+
+char const* set_error(rb_error_t* error, std::string msg) {
+    g_error = std::move(msg);
+    if (error)
+        *error = g_error.c_str();
+    return g_error.c_str();
+}
+
+std::string format(char const* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    return buf;
+}
+
+#define RB_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (expr);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return format("CUDA error %s at %s:%d (%s)", cudaGetErrorName(e_), __FILE__, __LINE__,      \
+                          cudaGetErrorString(e_));                                                      \
+    } while (0)
+
+size_t ceil2(size_t v) {
+    size_t r = 1;
+    while (r < v)
+        r <<= 1;
+    return r;
+}
+
+struct DeviceState {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    int sm_count = 0;
+    // graph + fingerprints
+    uint4* fp = nullptr;
+    uint32_t* adj0 = nullptr;
+    uint32_t* adju = nullptr;
+    uint32_t* upper_off = nullptr;
+    int8_t* levels = nullptr;
+    uint32_t* task_rel = nullptr;
+    size_t cap_rows = 0, cap_upper = 0;
+    size_t rows = 0, upper_rows = 0;  // what the device currently holds
+    // per-batch scratch
+    uint64_t* pair_keys[2] = {nullptr, nullptr};
+    uint64_t* pair_vals[2] = {nullptr, nullptr};
+    size_t pair_cap = 0;
+    void* sort_tmp = nullptr;
+    size_t sort_tmp_bytes = 0;
+    unsigned int* work_counters = nullptr;
+    size_t work_counters_cap = 0;
+    unsigned long long* counters = nullptr;  // [0] distances [1] expansions
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    int insert_blocks_per_sm = 0, search_blocks_per_sm = 0;
+    uint32_t insert_cfg_ef = 0, search_cfg_ef = 0;
+    void* scratch = nullptr;  // grow-only arena for query / result staging
+    size_t scratch_bytes = 0;
+
+    ~DeviceState() { release(); }
+    void release() {
+        if (device < 0)
+            return;
+        cudaSetDevice(device);
+        cudaFree(fp);
+        cudaFree(adj0);
+        cudaFree(adju);
+        cudaFree(upper_off);
+        cudaFree(levels);
+        cudaFree(task_rel);
+        for (int i = 0; i < 2; ++i) {
+            cudaFree(pair_keys[i]);
+            cudaFree(pair_vals[i]);
+        }
+        cudaFree(sort_tmp);
+        cudaFree(work_counters);
+        cudaFree(counters);
+        cudaFree(scratch);
+        if (ev_begin)
+            cudaEventDestroy(ev_begin);
+        if (ev_end)
+            cudaEventDestroy(ev_end);
+        if (stream)
+            cudaStreamDestroy(stream);
+        *this = DeviceState{};
+    }
+    DeviceState() = default;
+    DeviceState(DeviceState const&) = default;
+    DeviceState& operator=(DeviceState const&) = default;
+};
+
+}  // namespace
+
+struct rb_index {
+    rbh::HostIndex host;
+    DeviceState dev;
+    rb_init_options_t opts{};
+    bool device_graph_valid = false;  // the device holds the current graph and fingerprints
+    bool host_graph_valid = true;     // the host arrays hold the current graph
+    rb_counters_t last{};
+};
+
+namespace {
+
+std::string ensure_device(rb_index* ix) {
+    DeviceState& d = ix->dev;
+    if (d.device >= 0) {
+        RB_CUDA(cudaSetDevice(d.device));
+        return {};
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return "rad_b200 needs a CUDA device for add/search and found none (there is no CPU fallback)";
+    int dev = ix->opts.device;
+    if (dev < 0)
+        RB_CUDA(cudaGetDevice(&dev));
+    if (dev >= count)
+        return format("CUDA device %d requested but only %d present", dev, count);
+    RB_CUDA(cudaSetDevice(dev));
+    cudaDeviceProp prop;
+    RB_CUDA(cudaGetDeviceProperties(&prop, dev));
+    d.sm_count = prop.multiProcessorCount;
+    RB_CUDA(cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking));
+    RB_CUDA(cudaEventCreate(&d.ev_begin));
+    RB_CUDA(cudaEventCreate(&d.ev_end));
+    RB_CUDA(cudaMalloc(&d.counters, 4 * sizeof(unsigned long long)));
+    d.device = dev;
+    return {};
+}
+
+template <typename T>
+std::string grow_array(T*& ptr, size_t old_count, size_t new_count, int fill_byte, cudaStream_t stream) {
+    T* fresh = nullptr;
+    RB_CUDA(cudaMalloc(&fresh, std::max<size_t>(new_count, 1) * sizeof(T)));
+    if (old_count)
+        RB_CUDA(cudaMemcpyAsync(fresh, ptr, old_count * sizeof(T), cudaMemcpyDeviceToDevice, stream));
+    if (new_count > old_count)
+        RB_CUDA(cudaMemsetAsync(fresh + old_count, fill_byte, (new_count - old_count) * sizeof(T), stream));
+    RB_CUDA(cudaStreamSynchronize(stream));
+    cudaFree(ptr);
+    ptr = fresh;
+    return {};
+}
+
+std::string ensure_capacity(rb_index* ix, size_t rows, size_t upper) {
+    DeviceState& d = ix->dev;
+    const uint32_t m = ix->host.m, m0 = ix->host.m0;
+    if (rows > d.cap_rows) {
+        size_t cap = std::max(ceil2(rows), (size_t)1024);
+        std::string err;
+        if (!(err = grow_array(d.fp, d.cap_rows * 8, cap * 8, 0, d.stream)).empty()) return err;
+        if (!(err = grow_array(d.adj0, d.cap_rows * m0, cap * m0, 0xFF, d.stream)).empty()) return err;
+        if (!(err = grow_array(d.upper_off, d.cap_rows, cap, 0, d.stream)).empty()) return err;
+        if (!(err = grow_array(d.levels, d.cap_rows, cap, 0, d.stream)).empty()) return err;
+        if (!(err = grow_array(d.task_rel, d.cap_rows, cap, 0, d.stream)).empty()) return err;
+        d.cap_rows = cap;
+    }
+    if (upper > d.cap_upper) {
+        size_t cap = std::max(ceil2(upper), (size_t)1024);
+        std::string err = grow_array(d.adju, d.cap_upper * m, cap * m, 0xFF, d.stream);
+        if (!err.empty()) return err;
+        d.cap_upper = cap;
+    }
+    ix->host.capacity = std::max(ix->host.capacity, d.cap_rows);
+    return {};
+}
+
+// copy host rows [first, first + count) of a (count x vec_bytes, stride) matrix into 128-byte device rows
+std::string upload_rows(rb_index* ix, uint8_t const* src, size_t count, size_t stride, size_t first) {
+    DeviceState& d = ix->dev;
+    if (!count)
+        return {};
+    uint8_t* dst = reinterpret_cast<uint8_t*>(d.fp) + first * 128;
+    const size_t vb = ix->host.vec_bytes;
+    if (vb == 128 && stride == 128) {
+        RB_CUDA(cudaMemcpyAsync(dst, src, count * 128, cudaMemcpyHostToDevice, d.stream));
+    } else {
+        RB_CUDA(cudaMemsetAsync(dst, 0, count * 128, d.stream));
+        RB_CUDA(cudaMemcpy2DAsync(dst, 128, src, stride, vb, count, cudaMemcpyHostToDevice, d.stream));
+    }
+    return {};
+}
+
+// after rb_load: push the host graph and fingerprints to the device
+std::string upload_graph(rb_index* ix) {
+    rbh::HostIndex& h = ix->host;
+    DeviceState& d = ix->dev;
+    const size_t n = h.keys.size();
+    if (ix->device_graph_valid)
+        return {};
+    if (n && h.host_vectors.empty())
+        return "The fingerprints of this index are not available (loaded with exclude_vectors)";
+    std::string err = ensure_capacity(ix, n, h.upper_off[n]);
+    if (!err.empty())
+        return err;
+    if (n) {
+        if (!(err = upload_rows(ix, h.host_vectors.data(), n, h.vec_bytes, 0)).empty())
+            return err;
+        RB_CUDA(cudaMemcpyAsync(d.adj0, h.adj0.data(), n * h.m0 * 4, cudaMemcpyHostToDevice, d.stream));
+        if (h.upper_off[n])
+            RB_CUDA(cudaMemcpyAsync(d.adju, h.adju.data(), h.upper_off[n] * h.m * 4, cudaMemcpyHostToDevice, d.stream));
+        std::vector<uint32_t> off32(n);
+        std::vector<int8_t> lv8(n);
+        for (size_t i = 0; i < n; ++i) {
+            off32[i] = (uint32_t)h.upper_off[i];
+            lv8[i] = (int8_t)h.levels[i];
+        }
+        RB_CUDA(cudaMemcpyAsync(d.upper_off, off32.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
+        RB_CUDA(cudaMemcpyAsync(d.levels, lv8.data(), n, cudaMemcpyHostToDevice, d.stream));
+        RB_CUDA(cudaStreamSynchronize(d.stream));
+    }
+    d.rows = n;
+    d.upper_rows = h.upper_off[n];
+    ix->device_graph_valid = true;
+    h.host_vectors.clear();
+    h.host_vectors.shrink_to_fit();
+    return {};
+}
+
+std::string sync_host(rb_index* ix) {
+    if (ix->host_graph_valid)
+        return {};
+    rbh::HostIndex& h = ix->host;
+    DeviceState& d = ix->dev;
+    const size_t n = h.keys.size();
+    RB_CUDA(cudaSetDevice(d.device));
+    h.adj0.resize(n * (size_t)h.m0);
+    h.adju.resize(h.upper_off[n] * (size_t)h.m);
+    if (n)
+        RB_CUDA(cudaMemcpyAsync(h.adj0.data(), d.adj0, h.adj0.size() * 4, cudaMemcpyDeviceToHost, d.stream));
+    if (!h.adju.empty())
+        RB_CUDA(cudaMemcpyAsync(h.adju.data(), d.adju, h.adju.size() * 4, cudaMemcpyDeviceToHost, d.stream));
+    RB_CUDA(cudaStreamSynchronize(d.stream));
+    ix->host_graph_valid = true;
+    return {};
+}
+
+}  // namespace
+
+// ================================================================================================ build
+namespace {
+
+struct Batch {
+    uint32_t start, size;
+    uint32_t entry;
+    int32_t max_level;
+    uint32_t tasks;
+};
+
+// The schedule is a pure function of (current size, levels): mirrored by tests/model/batched_model.c.
+void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all_levels /* old + new */,
+                  std::vector<Batch>& batches, std::vector<uint32_t>& task_rel /* per new node */,
+                  int32_t& max_level, uint64_t& entry) {
+    const size_t total = all_levels.size();
+    const uint32_t den = ix->opts.batch_growth_den, bmax = ix->opts.batch_max;
+    size_t s = old_size;
+    task_rel.assign(total - old_size, 0);
+    while (s < total) {
+        if (ix->opts.debug_max_batches && batches.size() >= ix->opts.debug_max_batches)
+            break;
+        if (s == 0) {
+            batches.push_back(Batch{0, 1, 0, -1, 0});  // the first node only becomes the entry point
+            entry = 0;
+            max_level = all_levels[0];
+            s = 1;
+            continue;
+        }
+        size_t b = std::max<size_t>(1, s / den);
+        b = std::min<size_t>(b, bmax);
+        b = std::min(b, total - s);
+        bool raised = false;
+        int32_t run_max = max_level;
+        for (size_t t = 0; t < b; ++t) {
+            if (all_levels[s + t] > run_max) {
+                if (raised) {
+                    b = t;
+                    break;
+                }
+                raised = true;
+                run_max = all_levels[s + t];
+            }
+        }
+        uint32_t tasks = 0;
+        for (size_t t = 0; t < b; ++t) {
+            task_rel[s + t - old_size] = tasks;
+            tasks += (uint32_t)(std::min<int32_t>(all_levels[s + t], max_level) + 1);
+        }
+        batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, tasks});
+        for (size_t t = 0; t < b; ++t)
+            if (all_levels[s + t] > max_level) {
+                max_level = all_levels[s + t];
+                entry = s + t;
+            }
+        s += b;
+    }
+}
+
+std::string configure_traversal_kernels(rb_index* ix) {
+    DeviceState& d = ix->dev;
+    const uint32_t bloom = ix->opts.bloom_bits_log2, m = ix->host.m;
+    if (d.insert_cfg_ef != ix->host.ef_add) {
+        size_t smem = rb::warp_scratch_bytes(ix->host.ef_add, bloom, m) * rb::kWarpsPerBlock;
+        RB_CUDA(cudaFuncSetAttribute(rb::insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.insert_blocks_per_sm, rb::insert_kernel,
+                                                              rb::kWarpsPerBlock * 32, smem));
+        if (d.insert_blocks_per_sm < 1)
+            return "expansion_add does not fit the shared memory of one SM";
+        d.insert_cfg_ef = ix->host.ef_add;
+    }
+    return {};
+}
+
+std::string configure_search_kernel(rb_index* ix, uint32_t ef) {
+    DeviceState& d = ix->dev;
+    if (d.search_cfg_ef != ef) {
+        size_t smem = rb::warp_scratch_bytes(ef, ix->opts.bloom_bits_log2, ix->host.m) * rb::kWarpsPerBlock;
+        RB_CUDA(cudaFuncSetAttribute(rb::search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        RB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.search_blocks_per_sm, rb::search_kernel,
+                                                              rb::kWarpsPerBlock * 32, smem));
+        if (d.search_blocks_per_sm < 1)
+            return "expansion_search does not fit the shared memory of one SM";
+        d.search_cfg_ef = ef;
+    }
+    return {};
+}
+
+rb::GraphView graph_view(rb_index* ix) {
+    rb::GraphView g;
+    g.fp = ix->dev.fp;
+    g.adj0 = ix->dev.adj0;
+    g.adju = ix->dev.adju;
+    g.upper_off = ix->dev.upper_off;
+    g.m = ix->host.m;
+    g.m0 = ix->host.m0;
+    return g;
+}
+
+// shared tail of rb_add / rb_add_device: the fingerprints of the new rows are already enqueued on the stream
+std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::vector<int16_t>& new_levels,
+                           rb_progress_t progress, void* user, size_t& accepted) {
+    rbh::HostIndex& h = ix->host;
+    DeviceState& d = ix->dev;
+    const size_t old_size = h.keys.size();
+    accepted = 0;
+
+    std::vector<int16_t> all_levels(h.levels);
+    all_levels.insert(all_levels.end(), new_levels.begin(), new_levels.end());
+    std::vector<Batch> batches;
+    std::vector<uint32_t> task_rel;
+    int32_t max_level = h.max_level;
+    uint64_t entry = h.entry;
+    plan_batches(ix, old_size, all_levels, batches, task_rel, max_level, entry);
+
+    // per-node metadata of the new rows
+    std::vector<uint32_t> off32(n);
+    std::vector<int8_t> lv8(n);
+    uint64_t upper = h.upper_off[old_size];
+    for (size_t i = 0; i < n; ++i) {
+        off32[i] = (uint32_t)upper;
+        lv8[i] = (int8_t)new_levels[i];
+        upper += (uint64_t)new_levels[i];
+    }
+    RB_CUDA(cudaMemcpyAsync(d.upper_off + old_size, off32.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
+    RB_CUDA(cudaMemcpyAsync(d.levels + old_size, lv8.data(), n, cudaMemcpyHostToDevice, d.stream));
+    RB_CUDA(cudaMemcpyAsync(d.task_rel + old_size, task_rel.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
+
+    // scratch sized for the largest batch
+    size_t max_pairs = 0;
+    for (Batch const& b : batches)
+        max_pairs = std::max(max_pairs, (size_t)b.tasks * h.m);
+    if (max_pairs > d.pair_cap) {
+        size_t cap = ceil2(max_pairs);
+        for (int i = 0; i < 2; ++i) {
+            cudaFree(d.pair_keys[i]);
+            cudaFree(d.pair_vals[i]);
+            RB_CUDA(cudaMalloc(&d.pair_keys[i], cap * 8));
+            RB_CUDA(cudaMalloc(&d.pair_vals[i], cap * 8));
+        }
+        size_t tmp = 0;
+        RB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, d.pair_keys[0], d.pair_keys[1], d.pair_vals[0],
+                                                d.pair_vals[1], (int64_t)cap, 0, 40, d.stream));
+        if (tmp > d.sort_tmp_bytes) {
+            cudaFree(d.sort_tmp);
+            RB_CUDA(cudaMalloc(&d.sort_tmp, tmp));
+            d.sort_tmp_bytes = tmp;
+        }
+        d.pair_cap = cap;
+    }
+    if (batches.size() > d.work_counters_cap) {
+        cudaFree(d.work_counters);
+        d.work_counters_cap = ceil2(batches.size());
+        RB_CUDA(cudaMalloc(&d.work_counters, d.work_counters_cap * sizeof(unsigned int)));
+    }
+    RB_CUDA(cudaMemsetAsync(d.work_counters, 0, std::max<size_t>(batches.size(), 1) * sizeof(unsigned int), d.stream));
+    RB_CUDA(cudaMemsetAsync(d.counters, 0, 4 * sizeof(unsigned long long), d.stream));
+
+    std::string err = configure_traversal_kernels(ix);
+    if (!err.empty())
+        return err;
+    const size_t smem = rb::warp_scratch_bytes(h.ef_add, ix->opts.bloom_bits_log2, h.m) * rb::kWarpsPerBlock;
+    const rb::GraphView g = graph_view(ix);
+    uint64_t launches = 0;
+    size_t inserted = 0;
+    bool cancelled = false;
+    std::vector<cudaEvent_t> marks;  // progress marks
+    size_t next_mark = 0;
+    RB_CUDA(cudaEventRecord(d.ev_begin, d.stream));
+    for (size_t bi = 0; bi < batches.size(); ++bi) {
+        Batch const& b = batches[bi];
+        if (b.max_level >= 0) {
+            rb::InsertParams ip;
+            ip.g = g;
+            ip.levels = d.levels;
+            ip.task_rel = d.task_rel;
+            ip.pair_keys = d.pair_keys[0];
+            ip.pair_vals = d.pair_vals[0];
+            ip.batch_start = b.start;
+            ip.batch_size = b.size;
+            ip.entry = b.entry;
+            ip.max_level = b.max_level;
+            ip.ef = h.ef_add;
+            ip.bloom_log2 = ix->opts.bloom_bits_log2;
+            ip.work_counter = d.work_counters + bi;
+            ip.counters = d.counters;
+            unsigned blocks = (unsigned)std::min<size_t>((b.size + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
+                                                         (size_t)d.sm_count * d.insert_blocks_per_sm);
+            rb::insert_kernel<<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
+            const size_t pairs = (size_t)b.tasks * h.m;
+            size_t tmp = d.sort_tmp_bytes;
+            RB_CUDA(cub::DeviceRadixSort::SortPairs(d.sort_tmp, tmp, d.pair_keys[0], d.pair_keys[1], d.pair_vals[0],
+                                                    d.pair_vals[1], (int64_t)pairs, 0, 40, d.stream));
+            rb::ReverseParams rp;
+            rp.g = g;
+            rp.pair_keys = d.pair_keys[1];
+            rp.pair_vals = d.pair_vals[1];
+            rp.pair_count = (uint32_t)pairs;
+            rp.counters = d.counters;
+            unsigned rblocks = (unsigned)((pairs + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock);
+            rb::reverse_link_kernel<<<rblocks, rb::kWarpsPerBlock * 32, 0, d.stream>>>(rp);
+            launches += 2 + 4;  // ours + the radix-sort passes over 40 key bits (library code)
+            RB_CUDA(cudaGetLastError());
+        }
+        inserted += b.size;
+        if (progress && (bi % 8 == 7 || bi + 1 == batches.size())) {
+            cudaEvent_t ev;
+            RB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            RB_CUDA(cudaEventRecord(ev, d.stream));
+            marks.push_back(ev);
+            // report whatever has completed so far without blocking the launch loop
+            while (next_mark < marks.size() && cudaEventQuery(marks[next_mark]) == cudaSuccess)
+                ++next_mark;
+            size_t done_batches = next_mark ? std::min(batches.size(), next_mark * 8) : 0;
+            size_t done_rows = 0;
+            for (size_t t = 0; t < done_batches; ++t)
+                done_rows += batches[t].size;
+            if (!progress(done_rows, n, user)) {
+                cancelled = true;
+                break;
+            }
+        }
+    }
+    RB_CUDA(cudaEventRecord(d.ev_end, d.stream));
+    RB_CUDA(cudaStreamSynchronize(d.stream));
+    for (cudaEvent_t ev : marks)
+        cudaEventDestroy(ev);
+    RB_CUDA(cudaGetLastError());
+    float ms = 0;
+    RB_CUDA(cudaEventElapsedTime(&ms, d.ev_begin, d.ev_end));
+    unsigned long long counters[4];
+    RB_CUDA(cudaMemcpy(counters, d.counters, sizeof(counters), cudaMemcpyDeviceToHost));
+    ix->last.computed_distances = counters[0];
+    ix->last.visited_members = counters[1];
+    ix->last.batches = batches.size();
+    ix->last.kernel_launches = launches;
+    ix->last.device_ms = ms;
+
+    // commit what was inserted (everything unless a debug cap or a cancellation cut the schedule short)
+    accepted = inserted;
+    max_level = h.max_level;
+    entry = h.entry;
+    for (size_t i = 0; i < accepted; ++i) {
+        size_t slot = old_size + i;
+        if (slot == 0 || new_levels[i] > max_level) {
+            max_level = new_levels[i];
+            entry = slot;
+        }
+    }
+    h.keys.insert(h.keys.end(), keys, keys + accepted);
+    h.levels.insert(h.levels.end(), new_levels.begin(), new_levels.begin() + accepted);
+    h.upper_off.resize(old_size + accepted + 1);
+    for (size_t i = 0; i < accepted; ++i)
+        h.upper_off[old_size + i + 1] = h.upper_off[old_size + i] + (uint64_t)new_levels[i];
+    h.max_level = max_level;
+    h.entry = entry;
+    h.note_new_keys(keys, accepted);
+    d.rows = old_size + accepted;
+    d.upper_rows = h.upper_off[old_size + accepted];
+    ix->device_graph_valid = true;
+    ix->host_graph_valid = false;
+    if (progress)
+        progress(accepted, n, user);
+    if (cancelled)
+        return "Operation has been terminated";
+    return {};
+}
+
+std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_vectors, size_t stride,
+                       void const* device_vectors, size_t n, rb_progress_t progress, void* user) {
+    rbh::HostIndex& h = ix->host;
+    if (h.immutable())
+        return "Can't add to an immutable index";
+    if (!n)
+        return {};
+    const size_t old_size = h.keys.size();
+    if (old_size + n >= (1ull << 31))
+        return "rad_b200 addresses at most 2^31 - 1 fingerprints per index (shard larger sets by rows)";
+    std::vector<uint64_t> generated;
+    if (!keys) {
+        generated.resize(n);
+        for (size_t i = 0; i < n; ++i)
+            generated[i] = old_size + i;
+        keys = generated.data();
+    }
+    if (h.check_new_keys(keys, n) >= 0)
+        return "Duplicate keys not allowed in high-level wrappers";
+    std::string err = ensure_device(ix);
+    if (!err.empty())
+        return err;
+    if (!(err = upload_graph(ix)).empty())
+        return err;
+    std::vector<int16_t> new_levels;
+    const uint32_t rng_before = h.level_rng;
+    h.draw_levels(n, new_levels);
+    uint64_t upper = h.upper_off[old_size];
+    for (size_t i = 0; i < n; ++i)
+        upper += (uint64_t)new_levels[i];
+    if (upper >= (1ull << 32))
+        return "too many upper-level rows";
+    if (!(err = ensure_capacity(ix, ceil2(old_size + n), upper)).empty())
+        return err;
+    DeviceState& d = ix->dev;
+    if (device_vectors) {
+        RB_CUDA(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(d.fp) + old_size * 128, device_vectors, n * 128,
+                                cudaMemcpyDeviceToDevice, d.stream));
+    } else if (!(err = upload_rows(ix, host_vectors, n, stride, old_size)).empty()) {
+        return err;
+    }
+    // rows of the new nodes must start empty (a re-used capacity region may hold an aborted build)
+    RB_CUDA(cudaMemsetAsync(d.adj0 + old_size * h.m0, 0xFF, n * (size_t)h.m0 * 4, d.stream));
+    if (upper > h.upper_off[old_size])
+        RB_CUDA(cudaMemsetAsync(d.adju + h.upper_off[old_size] * h.m, 0xFF,
+                                (upper - h.upper_off[old_size]) * (size_t)h.m * 4, d.stream));
+    size_t accepted = 0;
+    err = build_new_rows(ix, keys, n, new_levels, progress, user, accepted);
+    if (accepted < n) {
+        // the level stream only advances over nodes that exist
+        h.level_rng = rng_before;
+        std::vector<int16_t> replay;
+        h.draw_levels(accepted, replay);
+    }
+    if (!err.empty())
+        return err;
+    if (!(ix->opts.flags & RB_FLAG_LAZY_HOST_SYNC))
+        return sync_host(ix);
+    return {};
+}
+
+}  // namespace
+
+// ================================================================================================ search
+namespace {
+
+struct ExactPlan {
+    uint32_t chunks;
+    uint64_t chunk_rows;
+    size_t keys_bytes, iu_bytes;
+};
+
+ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
+    ExactPlan p;
+    uint64_t qtiles = std::max<uint64_t>(1, (nq + rb::kXQ - 1) / rb::kXQ);
+    uint64_t row_tiles = std::max<uint64_t>(1, (rows + rb::kXD - 1) / rb::kXD);
+    uint64_t want = std::max<uint64_t>(1, (1184 + qtiles - 1) / qtiles);  // about 4 waves of 148 x 2 CTAs
+    uint64_t chunks = std::min(want, row_tiles);
+    uint64_t tiles_per_chunk = (row_tiles + chunks - 1) / chunks;
+    p.chunk_rows = tiles_per_chunk * rb::kXD;
+    p.chunks = (uint32_t)((row_tiles + tiles_per_chunk - 1) / tiles_per_chunk);
+    p.keys_bytes = ((size_t)p.chunks * nq * k * 8 + 255) & ~(size_t)255;
+    p.iu_bytes = ((size_t)p.chunks * nq * k * 4 + 255) & ~(size_t)255;
+    return p;
+}
+
+std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uint4 const* queries, uint64_t nq,
+                         uint32_t k, uint64_t* keys_out, void* workspace, size_t workspace_bytes,
+                         cudaStream_t stream) {
+    if (!nq)
+        return {};
+    if (k == 0 || k > 1024)
+        return "k must be in 1..1024";
+    if (slot_base + rows > (1ull << 32))
+        return "exact search addresses at most 2^32 slots";
+    ExactPlan pl = plan_exact(rows, nq, k);
+    if (workspace_bytes < pl.keys_bytes + pl.iu_bytes)
+        return "workspace too small (see rb_exact_topk_workspace_bytes)";
+    static bool configured = false;
+    if (!configured) {
+        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)sizeof(rb::ExactSmem)));
+        configured = true;
+    }
+    rb::ExactParams ep;
+    ep.db = db;
+    ep.queries = queries;
+    ep.rows = rows;
+    ep.slot_base = slot_base;
+    ep.query_count = (uint32_t)nq;
+    ep.k = k;
+    ep.chunks = pl.chunks;
+    ep.chunk_rows = pl.chunk_rows;
+    ep.partial_keys = static_cast<uint64_t*>(workspace);
+    ep.partial_iu = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(workspace) + pl.keys_bytes);
+    dim3 grid(pl.chunks, (unsigned)((nq + rb::kXQ - 1) / rb::kXQ));
+    rb::exact_topk_kernel<<<grid, rb::kXThreads, sizeof(rb::ExactSmem), stream>>>(ep);
+    rb::MergeParams mp;
+    mp.partial_keys = ep.partial_keys;
+    mp.parts = pl.chunks;
+    mp.query_count = (uint32_t)nq;
+    mp.k = k;
+    mp.keys_out = keys_out;
+    rb::merge_topk_kernel<<<(unsigned)((nq + 3) / 4), 128, 4 * (size_t)k * 8, stream>>>(mp);
+    RB_CUDA(cudaGetLastError());
+    return {};
+}
+
+__global__ void unpack_topk32_kernel(const uint64_t* keys, uint64_t query_count, uint32_t k, uint64_t slot_base,
+                                     uint32_t* slots, float* dists, int32_t* counts) {
+    uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= query_count)
+        return;
+    uint32_t cnt = 0;
+    for (uint32_t j = 0; j < k; ++j) {
+        uint64_t key = keys[q * k + j];
+        if (key == ~0ull)
+            break;
+        slots[q * k + j] = (uint32_t)(~(uint32_t)key - (uint32_t)slot_base);
+        dists[q * k + j] = __uint_as_float((uint32_t)(key >> 32));
+        ++cnt;
+    }
+    counts[q] = (int32_t)cnt;
+}
+
+std::string ensure_scratch(DeviceState& d, size_t bytes) {
+    if (bytes <= d.scratch_bytes)
+        return {};
+    cudaFree(d.scratch);
+    d.scratch = nullptr;
+    d.scratch_bytes = 0;
+    RB_CUDA(cudaMalloc(&d.scratch, bytes));
+    d.scratch_bytes = bytes;
+    return {};
+}
+
+// queries already on the device (padded rows); results into device buffers: slots u32, dists f32, counts i32
+std::string search_on_device(rb_index* ix, uint4 const* d_queries, size_t nq, size_t k, bool exact, uint32_t* d_slots,
+                             float* d_dists, int32_t* d_counts, void* extra_scratch, size_t extra_bytes) {
+    rbh::HostIndex& h = ix->host;
+    DeviceState& d = ix->dev;
+    const size_t n = h.size();
+    RB_CUDA(cudaMemsetAsync(d.counters, 0, 4 * sizeof(unsigned long long), d.stream));
+    RB_CUDA(cudaEventRecord(d.ev_begin, d.stream));
+    uint64_t launches = 0;
+    if (exact) {
+        ExactPlan pl = plan_exact(n, nq, (uint32_t)k);
+        size_t need = pl.keys_bytes + pl.iu_bytes + nq * k * 8;
+        if (extra_bytes < need)
+            return "internal: scratch too small";
+        uint64_t* merged = reinterpret_cast<uint64_t*>(static_cast<uint8_t*>(extra_scratch) + pl.keys_bytes + pl.iu_bytes);
+        std::string err = launch_exact(d.fp, n, 0, d_queries, nq, (uint32_t)k, merged, extra_scratch,
+                                       pl.keys_bytes + pl.iu_bytes, d.stream);
+        if (!err.empty())
+            return err;
+        unpack_topk32_kernel<<<(unsigned)((nq + 127) / 128), 128, 0, d.stream>>>(merged, nq, (uint32_t)k, 0, d_slots,
+                                                                                 d_dists, d_counts);
+        launches = 3;
+    } else {
+        uint32_t ef = (uint32_t)std::max<size_t>(h.ef_search, k);
+        if (ef > 1024)
+            return "expansion_search (or k) above 1024 is not supported";
+        std::string err = configure_search_kernel(ix, ef);
+        if (!err.empty())
+            return err;
+        unsigned int* wc = reinterpret_cast<unsigned int*>(d.counters + 3);
+        rb::SearchParams sp;
+        sp.g = graph_view(ix);
+        sp.queries = d_queries;
+        sp.query_count = (uint32_t)nq;
+        sp.entry = (uint32_t)h.entry;
+        sp.max_level = h.max_level;
+        sp.ef = ef;
+        sp.k = (uint32_t)k;
+        sp.bloom_log2 = ix->opts.bloom_bits_log2;
+        sp.slots_out = d_slots;
+        sp.dists_out = d_dists;
+        sp.counts_out = d_counts;
+        sp.work_counter = wc;
+        sp.counters = d.counters;
+        size_t smem = rb::warp_scratch_bytes(ef, ix->opts.bloom_bits_log2, h.m) * rb::kWarpsPerBlock;
+        unsigned blocks = (unsigned)std::min<size_t>((nq + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
+                                                     (size_t)d.sm_count * d.search_blocks_per_sm);
+        rb::search_kernel<<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
+        launches = 1;
+    }
+    RB_CUDA(cudaGetLastError());
+    RB_CUDA(cudaEventRecord(d.ev_end, d.stream));
+    RB_CUDA(cudaStreamSynchronize(d.stream));
+    float ms = 0;
+    RB_CUDA(cudaEventElapsedTime(&ms, d.ev_begin, d.ev_end));
+    unsigned long long counters[4];
+    RB_CUDA(cudaMemcpy(counters, d.counters, sizeof(counters), cudaMemcpyDeviceToHost));
+    ix->last.computed_distances = exact ? (uint64_t)nq * n : counters[0];
+    ix->last.visited_members = exact ? 0 : counters[1];
+    ix->last.batches = 0;
+    ix->last.kernel_launches = launches;
+    ix->last.device_ms = ms;
+    return {};
+}
+
+size_t exact_scratch_bytes(size_t n, size_t nq, size_t k) {
+    ExactPlan pl = plan_exact(n, nq, (uint32_t)k);
+    return pl.keys_bytes + pl.iu_bytes + nq * k * 8 + 256;
+}
+
+std::string prepare_search(rb_index* ix, size_t k) {
+    rbh::HostIndex& h = ix->host;
+    if (!k)
+        return "k must be positive";
+    if (h.viewing) {
+        // a viewed index can be searched only if its fingerprints are mapped: materialise it on the device once
+        return "rad_b200 cannot search a viewed index; load() it instead (view serves graph reads only)";
+    }
+    std::string err = ensure_device(ix);
+    if (!err.empty())
+        return err;
+    return upload_graph(ix);
+}
+
+}  // namespace
+
+// ================================================================================================ C ABI
+#define RB_FAIL(msg)              \
+    do {                          \
+        set_error(error, (msg));  \
+        return;                   \
+    } while (0)
+
+extern "C" {
+
+char const* rb_version(void) { return "rad_b200 0.1 (usearch-file 2.17.2, sm_100a)"; }
+
+int rb_device_count(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess)
+        return 0;
+    return count;
+}
+
+rb_index_t* rb_init(rb_init_options_t const* options, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    rb_init_options_t o{};
+    if (options)
+        o = *options;
+    if (!o.dimensions)
+        o.dimensions = 1024;
+    if (o.dimensions % 8 != 0 || o.dimensions > 1024) {
+        set_error(error, "rad_b200 supports 8..1024-bit fingerprints (multiples of 8)");
+        return nullptr;
+    }
+    if (!o.connectivity)
+        o.connectivity = 16;
+    if (o.connectivity < 2 || o.connectivity > 16) {
+        set_error(error, "connectivity must be in 2..16");
+        return nullptr;
+    }
+    if (!o.expansion_add)
+        o.expansion_add = 128;
+    if (!o.expansion_search)
+        o.expansion_search = 64;
+    if (o.expansion_add > 1024 || o.expansion_search > 1024) {
+        set_error(error, "expansion factors above 1024 are not supported");
+        return nullptr;
+    }
+    if (!o.batch_growth_den)
+        o.batch_growth_den = 8;
+    if (!o.batch_max)
+        o.batch_max = 65536;
+    if (!o.bloom_bits_log2)
+        o.bloom_bits_log2 = 16;
+    if (o.bloom_bits_log2 < 10 || o.bloom_bits_log2 > 18) {
+        set_error(error, "bloom_bits_log2 must be in 10..18");
+        return nullptr;
+    }
+    rb_index* ix = new rb_index();
+    ix->opts = o;
+    ix->host.ndim = o.dimensions;
+    ix->host.vec_bytes = (uint32_t)(o.dimensions / 8);
+    ix->host.m = o.connectivity;
+    ix->host.m0 = 2 * o.connectivity;
+    ix->host.ef_add = o.expansion_add;
+    ix->host.ef_search = o.expansion_search;
+    ix->host.upper_off.assign(1, 0);
+    return ix;
+}
+
+void rb_free(rb_index_t* index) { delete index; }
+
+void rb_release_device(rb_index_t* ix, int keep_host_vectors, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (ix->dev.device < 0)
+        return;
+    std::string err = sync_host(ix);
+    if (!err.empty())
+        RB_FAIL(err);
+    if (keep_host_vectors && ix->device_graph_valid && ix->host.keys.size()) {
+        rbh::HostIndex& h = ix->host;
+        h.host_vectors.resize(h.keys.size() * (size_t)h.vec_bytes);
+        cudaError_t e = cudaMemcpy2D(h.host_vectors.data(), h.vec_bytes, ix->dev.fp, 128, h.vec_bytes, h.keys.size(),
+                                     cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess)
+            RB_FAIL(std::string("CUDA error while fetching fingerprints: ") + cudaGetErrorString(e));
+    }
+    ix->dev.release();
+    ix->device_graph_valid = false;
+}
+
+void rb_reserve(rb_index_t* ix, size_t capacity, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (ix->host.immutable())
+        RB_FAIL("Can't reserve on an immutable index");
+    std::string err = ensure_device(ix);
+    if (err.empty())
+        err = upload_graph(ix);
+    if (err.empty())
+        err = ensure_capacity(ix, capacity, std::max<size_t>(ix->host.upper_off.back(), capacity / 4));
+    if (!err.empty())
+        RB_FAIL(err);
+    ix->host.capacity = std::max(ix->host.capacity, capacity);
+}
+
+void rb_add(rb_index_t* ix, uint64_t const* keys, uint8_t const* vectors, size_t count, size_t row_stride_bytes,
+            int copy, rb_progress_t progress, void* progress_user, rb_error_t* error) {
+    (void)copy;  // the index always owns a device copy (index_dense.hpp:2134-2139 allows either)
+    if (error)
+        *error = nullptr;
+    if (count && !vectors)
+        RB_FAIL("Expects a matrix of vectors to add!");
+    if (row_stride_bytes < ix->host.vec_bytes)
+        RB_FAIL("The number of vector dimensions doesn't match!");
+    std::string err = add_common(ix, keys, vectors, row_stride_bytes, nullptr, count, progress, progress_user);
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+void rb_add_device(rb_index_t* ix, uint64_t const* keys, void const* d_vectors, size_t count, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (count && !d_vectors)
+        RB_FAIL("Expects a matrix of vectors to add!");
+    std::string err = add_common(ix, keys, nullptr, 128, d_vectors, count, nullptr, nullptr);
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+void rb_sync_host(rb_index_t* ix, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    std::string err = sync_host(ix);
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+void rb_search(rb_index_t* ix, uint8_t const* queries, size_t nq, size_t stride, size_t k, int exact,
+               uint64_t* keys_out, float* distances_out, int64_t* counts_out, uint64_t* visited_members,
+               uint64_t* computed_distances, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (visited_members)
+        *visited_members = 0;
+    if (computed_distances)
+        *computed_distances = 0;
+    if (!nq)
+        return;
+    rbh::HostIndex& h = ix->host;
+    if (stride < h.vec_bytes)
+        RB_FAIL("The number of vector dimensions doesn't match!");
+    if (!h.size()) {
+        for (size_t q = 0; q < nq; ++q)
+            counts_out[q] = 0;
+        return;
+    }
+    std::string err = prepare_search(ix, k);
+    if (!err.empty())
+        RB_FAIL(err);
+    DeviceState& d = ix->dev;
+    // arena: [queries | slots | dists | counts | exact workspace]
+    size_t q_bytes = (nq * 128 + 255) & ~(size_t)255;
+    size_t s_bytes = (nq * k * 4 + 255) & ~(size_t)255;
+    size_t c_bytes = (nq * 4 + 255) & ~(size_t)255;
+    size_t x_bytes = exact ? exact_scratch_bytes(h.size(), nq, k) : 0;
+    if (!(err = ensure_scratch(d, q_bytes + 2 * s_bytes + c_bytes + x_bytes)).empty())
+        RB_FAIL(err);
+    uint8_t* base = static_cast<uint8_t*>(d.scratch);
+    uint4* dq = reinterpret_cast<uint4*>(base);
+    uint32_t* ds = reinterpret_cast<uint32_t*>(base + q_bytes);
+    float* dd = reinterpret_cast<float*>(base + q_bytes + s_bytes);
+    int32_t* dc = reinterpret_cast<int32_t*>(base + q_bytes + 2 * s_bytes);
+    void* dx = base + q_bytes + 2 * s_bytes + c_bytes;
+    cudaError_t e;
+    if (h.vec_bytes == 128 && stride == 128) {
+        e = cudaMemcpyAsync(dq, queries, nq * 128, cudaMemcpyHostToDevice, d.stream);
+    } else {
+        e = cudaMemsetAsync(dq, 0, nq * 128, d.stream);
+        if (e == cudaSuccess)
+            e = cudaMemcpy2DAsync(dq, 128, queries, stride, h.vec_bytes, nq, cudaMemcpyHostToDevice, d.stream);
+    }
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error while uploading queries: ") + cudaGetErrorString(e));
+    if (!(err = search_on_device(ix, dq, nq, k, exact != 0, ds, dd, dc, dx, x_bytes)).empty())
+        RB_FAIL(err);
+    std::vector<uint32_t> slots(nq * k);
+    std::vector<float> dists(nq * k);
+    std::vector<int32_t> counts(nq);
+    e = cudaMemcpy(slots.data(), ds, nq * k * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess)
+        e = cudaMemcpy(dists.data(), dd, nq * k * 4, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess)
+        e = cudaMemcpy(counts.data(), dc, nq * 4, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error while fetching results: ") + cudaGetErrorString(e));
+    for (size_t q = 0; q < nq; ++q) {
+        int32_t c = counts[q];
+        counts_out[q] = c;
+        for (int32_t j = 0; j < c; ++j) {
+            keys_out[q * k + j] = h.keys[slots[q * k + j]];
+            distances_out[q * k + j] = dists[q * k + j];
+        }
+    }
+    if (visited_members)
+        *visited_members = ix->last.visited_members;
+    if (computed_distances)
+        *computed_distances = ix->last.computed_distances;
+}
+
+void rb_search_device(rb_index_t* ix, void const* d_queries, size_t nq, size_t k, int exact, void* d_slots_out,
+                      void* d_distances_out, void* d_counts_out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!nq)
+        return;
+    std::string err = prepare_search(ix, k);
+    if (!err.empty())
+        RB_FAIL(err);
+    if (!ix->host.size())
+        RB_FAIL("The index is empty");
+    size_t x_bytes = exact ? exact_scratch_bytes(ix->host.size(), nq, k) : 0;
+    if (!(err = ensure_scratch(ix->dev, x_bytes)).empty())
+        RB_FAIL(err);
+    err = search_on_device(ix, static_cast<uint4 const*>(d_queries), nq, k, exact != 0,
+                           static_cast<uint32_t*>(d_slots_out), static_cast<float*>(d_distances_out),
+                           static_cast<int32_t*>(d_counts_out), ix->dev.scratch, x_bytes);
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+size_t rb_exact_topk_workspace_bytes(uint64_t rows, uint64_t query_count, uint32_t k) {
+    ExactPlan pl = plan_exact(rows, query_count, k);
+    return pl.keys_bytes + pl.iu_bytes;
+}
+
+void rb_exact_topk_device(void const* d_database, uint64_t rows, uint64_t slot_base, void const* d_queries,
+                          uint64_t query_count, uint32_t k, void* d_keys_out, void* d_workspace,
+                          size_t workspace_bytes, uintptr_t stream, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    std::string err = launch_exact(static_cast<uint4 const*>(d_database), rows, slot_base,
+                                   static_cast<uint4 const*>(d_queries), query_count, k,
+                                   static_cast<uint64_t*>(d_keys_out), d_workspace, workspace_bytes,
+                                   reinterpret_cast<cudaStream_t>(stream));
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+void rb_merge_topk_device(void const* d_partial_keys, uint32_t parts, uint64_t query_count, uint32_t k,
+                          void* d_keys_out, uintptr_t stream, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!query_count)
+        return;
+    rb::MergeParams mp;
+    mp.partial_keys = static_cast<uint64_t const*>(d_partial_keys);
+    mp.parts = parts;
+    mp.query_count = (uint32_t)query_count;
+    mp.k = k;
+    mp.keys_out = static_cast<uint64_t*>(d_keys_out);
+    rb::merge_topk_kernel<<<(unsigned)((query_count + 3) / 4), 128, 4 * (size_t)k * 8,
+                            reinterpret_cast<cudaStream_t>(stream)>>>(mp);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in merge: ") + cudaGetErrorString(e));
+}
+
+void rb_unpack_topk_device(void const* d_keys, uint64_t query_count, uint32_t k, void* d_slots_out,
+                           void* d_distances_out, void* d_counts_out, uintptr_t stream, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!query_count)
+        return;
+    rb::unpack_topk_kernel<<<(unsigned)((query_count + 127) / 128), 128, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        static_cast<uint64_t const*>(d_keys), query_count, k, static_cast<uint64_t*>(d_slots_out),
+        static_cast<float*>(d_distances_out), static_cast<int64_t*>(d_counts_out));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in unpack: ") + cudaGetErrorString(e));
+}
+
+void rb_synth_fingerprints_device(void* d_out, uint64_t first_row, uint64_t rows, uint64_t seed, void const* d_centres,
+                                  uint32_t centre_count, int edge_cases, uintptr_t stream, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!rows)
+        return;
+    uint64_t threads = rows * 32;
+    rb::synth_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        static_cast<uint32_t*>(d_out), first_row, rows, seed, static_cast<uint32_t const*>(d_centres), centre_count,
+        edge_cases);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in synth: ") + cudaGetErrorString(e));
+}
+
+}  // extern "C"
+
+// ================================================================================================ C ABI, host side
+namespace {
+
+// fingerprints of the whole index as a host matrix (size x vec_bytes); empty when they live nowhere
+std::string fetch_vectors(rb_index* ix, std::vector<uint8_t>& out) {
+    rbh::HostIndex& h = ix->host;
+    const size_t n = h.size();
+    out.clear();
+    if (!n)
+        return {};
+    if (!h.host_vectors.empty()) {
+        out = h.host_vectors;
+        return {};
+    }
+    if (ix->device_graph_valid && ix->dev.device >= 0) {
+        RB_CUDA(cudaSetDevice(ix->dev.device));
+        out.resize(n * (size_t)h.vec_bytes);
+        RB_CUDA(cudaMemcpy2D(out.data(), h.vec_bytes, ix->dev.fp, 128, h.vec_bytes, n, cudaMemcpyDeviceToHost));
+        return {};
+    }
+    return "The fingerprints are not available";
+}
+
+}  // namespace
+
+extern "C" {
+
+void rb_save(rb_index_t* ix, char const* path, int exclude_vectors, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    std::string err = sync_host(ix);
+    if (!err.empty())
+        RB_FAIL(err);
+    std::vector<uint8_t> vectors;
+    uint8_t const* vptr = nullptr;
+    if (!exclude_vectors && !ix->host.viewing) {
+        if (!(err = fetch_vectors(ix, vectors)).empty())
+            RB_FAIL(err);
+        vptr = vectors.data();
+    }
+    err = ix->host.save(path, vptr, exclude_vectors != 0);
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+void rb_load(rb_index_t* ix, char const* path, int exclude_vectors, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    const uint32_t ef_add = ix->host.ef_add, ef_search = ix->host.ef_search;
+    std::string err = ix->host.load(path, exclude_vectors != 0);
+    ix->host.ef_add = ef_add;
+    ix->host.ef_search = ef_search;
+    ix->device_graph_valid = false;
+    ix->host_graph_valid = true;
+    ix->dev.rows = 0;
+    ix->dev.insert_cfg_ef = ix->dev.search_cfg_ef = 0;  // connectivity may have changed
+    if (!err.empty())
+        RB_FAIL(err);
+    if (ix->dev.device >= 0 && (ix->dev.cap_rows || ix->dev.cap_upper)) {
+        // row widths depend on the connectivity stored in the file: start from fresh device arrays
+        int dev = ix->dev.device;
+        ix->dev.release();
+        ix->opts.device = dev;
+    }
+}
+
+void rb_view(rb_index_t* ix, char const* path, int exclude_vectors, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    const uint32_t ef_add = ix->host.ef_add, ef_search = ix->host.ef_search;
+    std::string err = ix->host.view(path, exclude_vectors != 0);
+    ix->host.ef_add = ef_add;
+    ix->host.ef_search = ef_search;
+    ix->device_graph_valid = false;
+    ix->host_graph_valid = true;
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+void rb_metadata(char const* path, rb_metadata_t* out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    rbh::FileMetadata md;
+    std::string err = rbh::HostIndex::metadata(path, md);
+    if (!err.empty())
+        RB_FAIL(err);
+    out->version_major = md.version_major;
+    out->version_minor = md.version_minor;
+    out->version_patch = md.version_patch;
+    out->kind_metric = md.kind_metric;
+    out->kind_scalar = md.kind_scalar;
+    out->kind_key = md.kind_key;
+    out->kind_compressed_slot = md.kind_compressed_slot;
+    out->count_present = md.count_present;
+    out->count_deleted = md.count_deleted;
+    out->dimensions = md.dimensions;
+    out->multi = md.multi;
+    out->has_vectors = md.has_vectors;
+    out->matrix_rows = md.matrix_rows;
+    out->matrix_cols = md.matrix_cols;
+}
+
+size_t rb_neighbors(rb_index_t const* ix, size_t slot, int level, uint64_t* out_pairs, size_t capacity,
+                    rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!ix->host_graph_valid) {
+        set_error(error, "the host copy of the graph is stale: call rb_sync_host first");
+        return 0;
+    }
+    uint32_t tmp[64];
+    int cnt = ix->host.neighbors(slot, level, tmp, 64);
+    if (cnt == -1) {
+        set_error(error, format("Node %zu is out of range (size: %zu)", slot, ix->host.size()));
+        return 0;
+    }
+    if (cnt == -2) {
+        int node_level = slot < ix->host.size() ? ix->host.level_of(slot) : 0;
+        set_error(error, format("Level %d is out of range for node (max level: %d)", level, node_level));
+        return 0;
+    }
+    size_t written = 0;
+    for (int j = 0; j < cnt && written + 2 <= capacity; ++j) {
+        out_pairs[written++] = tmp[j];
+        out_pairs[written++] = ix->host.key_of(tmp[j]);
+    }
+    return written;
+}
+
+size_t rb_top_level_nodes(rb_index_t const* ix, uint64_t* out_pairs, size_t capacity, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    std::vector<uint32_t> top;
+    ix->host.top_level_nodes(top);
+    if (!out_pairs)
+        return top.size() * 2;
+    size_t written = 0;
+    for (size_t j = 0; j < top.size() && written + 2 <= capacity; ++j) {
+        out_pairs[written++] = top[j];
+        out_pairs[written++] = ix->host.key_of(top[j]);
+    }
+    return written;
+}
+
+void rb_keys_from_slots(rb_index_t const* ix, uint64_t const* slots, size_t count, uint64_t* keys_out,
+                        rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    const size_t n = ix->host.size();
+    for (size_t i = 0; i < count; ++i) {
+        if (slots[i] >= n)
+            RB_FAIL(format("Node %llu is out of range (size: %zu)", (unsigned long long)slots[i], n));
+        keys_out[i] = ix->host.key_of(slots[i]);
+    }
+}
+
+void rb_slots_from_keys(rb_index_t* ix, uint64_t const* keys, size_t count, int64_t* slots_out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    for (size_t i = 0; i < count; ++i)
+        slots_out[i] = ix->host.slot_of_key(keys[i]);
+}
+
+int rb_contains(rb_index_t* ix, uint64_t key) { return ix->host.slot_of_key(key) >= 0; }
+
+void rb_get_vectors(rb_index_t* ix, uint64_t const* slots, size_t count, uint8_t* out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    rbh::HostIndex& h = ix->host;
+    const size_t n = h.size(), vb = h.vec_bytes;
+    for (size_t i = 0; i < count; ++i)
+        if (slots[i] >= n)
+            RB_FAIL(format("Node %llu is out of range (size: %zu)", (unsigned long long)slots[i], n));
+    if (h.viewing) {
+        if (!h.viewed_vectors())
+            RB_FAIL("The fingerprints of this index are not available (viewed with exclude_vectors)");
+        for (size_t i = 0; i < count; ++i)
+            std::memcpy(out + i * vb, h.viewed_vectors() + slots[i] * vb, vb);
+        return;
+    }
+    if (!h.host_vectors.empty()) {
+        for (size_t i = 0; i < count; ++i)
+            std::memcpy(out + i * vb, h.host_vectors.data() + slots[i] * vb, vb);
+        return;
+    }
+    if (!ix->device_graph_valid || ix->dev.device < 0)
+        RB_FAIL("The fingerprints are not available");
+    cudaSetDevice(ix->dev.device);
+    for (size_t i = 0; i < count; ++i) {
+        cudaError_t e = cudaMemcpy(out + i * vb, reinterpret_cast<uint8_t const*>(ix->dev.fp) + slots[i] * 128, vb,
+                                   cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess)
+            RB_FAIL(std::string("CUDA error while fetching fingerprints: ") + cudaGetErrorString(e));
+    }
+}
+
+size_t rb_size(rb_index_t const* ix) { return ix->host.size(); }
+size_t rb_capacity(rb_index_t const* ix) { return std::max(ix->host.capacity, ix->host.size()); }
+int32_t rb_max_level(rb_index_t const* ix) { return ix->host.max_level; }
+uint64_t rb_entry_slot(rb_index_t const* ix) { return ix->host.entry; }
+size_t rb_connectivity(rb_index_t const* ix) { return ix->host.m; }
+size_t rb_dimensions(rb_index_t const* ix) { return ix->host.ndim; }
+size_t rb_memory_usage(rb_index_t const* ix) {
+    size_t device = 0;
+    DeviceState const& d = ix->dev;
+    if (d.device >= 0)
+        device = d.cap_rows * (128 + (size_t)ix->host.m0 * 4 + 4 + 1 + 4) + d.cap_upper * (size_t)ix->host.m * 4 +
+                 d.pair_cap * 32 + d.sort_tmp_bytes + d.scratch_bytes;
+    return ix->host.memory_usage() + device;
+}
+size_t rb_serialized_length(rb_index_t const* ix, int exclude_vectors) {
+    return ix->host.serialized_length(exclude_vectors != 0);
+}
+size_t rb_expansion_add(rb_index_t const* ix) { return ix->host.ef_add; }
+size_t rb_expansion_search(rb_index_t const* ix) { return ix->host.ef_search; }
+void rb_set_expansion_add(rb_index_t* ix, size_t expansion) {
+    ix->host.ef_add = (uint32_t)std::min<size_t>(std::max<size_t>(expansion, 1), 1024);
+}
+void rb_set_expansion_search(rb_index_t* ix, size_t expansion) {
+    ix->host.ef_search = (uint32_t)std::min<size_t>(std::max<size_t>(expansion, 1), 1024);
+}
+
+void rb_level_stats(rb_index_t const* ix, size_t level, rb_level_stats_t* out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!ix->host_graph_valid)
+        RB_FAIL("the host copy of the graph is stale: call rb_sync_host first");
+    rbh::LevelStats st;
+    if (!ix->host.level_stats(level, st))
+        RB_FAIL("The level is out of range");
+    out->nodes = st.nodes;
+    out->edges = st.edges;
+    out->max_edges = st.max_edges;
+    out->allocated_bytes = st.allocated_bytes;
+}
+
+void rb_levels(rb_index_t const* ix, int16_t* out, size_t capacity) {
+    size_t n = std::min(capacity, ix->host.size());
+    for (size_t i = 0; i < n; ++i)
+        out[i] = (int16_t)ix->host.level_of(i);
+}
+
+void rb_last_counters(rb_index_t const* ix, rb_counters_t* out) { *out = ix->last; }
+
+uint64_t rb_debug_adjacency(rb_index_t const* ix, uint32_t* adj0_out, uint32_t* adj_upper_out) {
+    rbh::HostIndex const& h = ix->host;
+    if (h.viewing || !ix->host_graph_valid)
+        return 0;
+    if (adj0_out)
+        std::memcpy(adj0_out, h.adj0.data(), h.adj0.size() * 4);
+    if (adj_upper_out)
+        std::memcpy(adj_upper_out, h.adju.data(), h.adju.size() * 4);
+    return h.upper_off[h.keys.size()];
+}
+
+}  // extern "C"

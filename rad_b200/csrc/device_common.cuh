@@ -1,0 +1,74 @@
+// device_common.cuh -- shared device primitives: Tanimoto counts on 128-byte fingerprints, order keys, warp helpers.
+//
+// Replaces the reference's innermost kernel simsimd_jaccard_b8_{serial,haswell,ice}
+// (usearch/simsimd/include/simsimd/binary.h:99-105, 349-444, 465-474) reached through metric_punned_t
+// (usearch/include/usearch/index_plugins.hpp:1691-1693, 1886-1893).
+//
+// Layout: one fingerprint = 128 bytes = 8 x uint4, 128-byte aligned (one L2 line).  A group of 8 lanes owns one
+// fingerprint (lane & 7 selects the 16-byte slice), so a warp reads 4 complete lines per LDG.128 instruction.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#define RB_EMPTY 0xFFFFFFFFu
+#define RB_FULL_MASK 0xFFFFFFFFu
+
+namespace rb {
+
+// Reference-exact distance bits: (float)(1.0 - (double)i / (double)u), u == 0 -> 1  (binary.h:104, index_plugins.hpp:1892).
+__device__ __forceinline__ uint32_t exact_distance_bits(uint32_t inter, uint32_t uni) {
+    double d = uni ? __dsub_rn(1.0, __ddiv_rn((double)inter, (double)uni)) : 1.0;
+    return __float_as_uint(__double2float_rn(d));
+}
+
+// Order key used inside graph traversal: 1.0f - RN(i / u) in f32.  Strictly monotone in the exact rational i/u and
+// equal for equal rationals (checked exhaustively for u <= 1024 in tests/test_order_key.py), so every comparison
+// agrees with the reference-exact bits, at a fraction of the cost of the f64 divide.  Never returned to callers.
+__device__ __forceinline__ uint32_t order_key_bits(uint32_t inter, uint32_t uni) {
+    float s = uni ? __fdiv_rn((float)inter, (float)uni) : 0.0f;
+    return __float_as_uint(__fsub_rn(1.0f, s));
+}
+
+__device__ __forceinline__ uint32_t popc4(uint4 v) { return __popc(v.x) + __popc(v.y) + __popc(v.z) + __popc(v.w); }
+__device__ __forceinline__ uint32_t popc4_and(uint4 a, uint4 b) {
+    return __popc(a.x & b.x) + __popc(a.y & b.y) + __popc(a.z & b.z) + __popc(a.w & b.w);
+}
+__device__ __forceinline__ uint32_t popc4_or(uint4 a, uint4 b) {
+    return __popc(a.x | b.x) + __popc(a.y | b.y) + __popc(a.z | b.z) + __popc(a.w | b.w);
+}
+
+// sum over the 8 lanes of a group (all 32 lanes must call)
+__device__ __forceinline__ uint32_t group8_sum(uint32_t v) {
+    v += __shfl_xor_sync(RB_FULL_MASK, v, 1);
+    v += __shfl_xor_sync(RB_FULL_MASK, v, 2);
+    v += __shfl_xor_sync(RB_FULL_MASK, v, 4);
+    return v;
+}
+
+// intersection | union << 16 of two fingerprints held slice-wise by a group of 8 lanes
+__device__ __forceinline__ uint32_t group8_inter_union(uint4 a, uint4 b) {
+    return group8_sum(popc4_and(a, b) | (popc4_or(a, b) << 16));
+}
+
+__device__ __forceinline__ uint4 load_slice(const uint4* __restrict__ fp, uint32_t slot, int sub) {
+    return __ldg(fp + (size_t)slot * 8 + sub);
+}
+
+struct GraphView {
+    const uint4* fp;            // rows x 8 uint4
+    uint32_t* adj0;             // rows x m0, RB_EMPTY padded
+    uint32_t* adju;             // upper rows x m
+    const uint32_t* upper_off;  // rows: first upper row of a node (levels 1..level are consecutive)
+    uint32_t m, m0;
+};
+
+__device__ __forceinline__ uint32_t* graph_row(const GraphView& g, uint32_t slot, int level, uint32_t& width) {
+    if (level == 0) {
+        width = g.m0;
+        return g.adj0 + (size_t)slot * g.m0;
+    }
+    width = g.m;
+    return g.adju + ((size_t)__ldg(g.upper_off + slot) + (uint32_t)(level - 1)) * g.m;
+}
+
+}  // namespace rb

@@ -1,0 +1,591 @@
+// hnsw_kernels.cuh -- warp-cooperative HNSW traversal, neighbour selection and batched link updates (sm_100a).
+//
+// What these kernels replace in the reference (usearch/include/usearch/index.hpp):
+//   warp_greedy_descent   search_for_one_            3935-3975
+//   warp_beam_search      search_to_insert_ / search_to_find_in_base_   3982-4051 / 4147-4217
+//                         (max_heap_gt `next` 659-830 + sorted_buffer_gt `top` 840-951 + growing_hash_set_gt visits
+//                          1080-1206 collapse into ONE sorted shared-memory list with an expanded bit per entry and
+//                          a shared-memory Bloom filter)
+//   warp_select_neighbors refine_                    4246-4289  (via form_links_to_closest_ 3793-3814)
+//   insert_kernel         index_gt::add              2734-2834  for a whole batch of nodes at once
+//   reverse_link_kernel   form_reverse_links_        3816-3865  merged per (level, target) instead of per-node locks
+//   search_kernel         index_gt::search           2970-3029  (approximate branch)
+//
+// One warp owns one query.  A fingerprint is fetched by a group of 8 lanes (one 128-byte line, LDG.128 per lane),
+// so every warp-wide load instruction brings 4 complete fingerprints; up to 16 are in flight per lane-group round.
+// The executable specification of these kernels is tests/model/batched_model.c (bit-exact graph parity).
+#pragma once
+#include "device_common.cuh"
+
+namespace rb {
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kMaxWidth = 32;      // 2 * max connectivity
+constexpr int kCandMax = 64;       // candidates considered when re-pruning a saturated list
+constexpr int kIncomingCap = 256;  // incoming reverse links examined per (level, target) and batch
+
+// key = order_key_bits << 32 | slot << 1 | expanded
+__device__ __forceinline__ uint64_t make_key(uint32_t bits, uint32_t slot) {
+    return ((uint64_t)bits << 32) | ((uint64_t)slot << 1);
+}
+__device__ __forceinline__ uint32_t key_slot(uint64_t key) { return (uint32_t)(key >> 1) & 0x7FFFFFFFu; }
+__device__ __forceinline__ uint32_t key_bits(uint64_t key) { return (uint32_t)(key >> 32); }
+
+struct WarpScratch {
+    uint64_t* list;    // ef entries
+    uint32_t* bloom;   // 2^bloom_log2 bits
+    uint4* kept;       // kMaxWidth fingerprints (32 x 8 uint4) for the selection heuristic
+    uint64_t* sel;     // kMaxWidth selected keys
+    uint32_t* ids;     // 32 staging ids
+    uint32_t bloom_log2;
+};
+
+// kept_rows = fingerprints the selection heuristic may keep (= connectivity in the insert / search kernels)
+__host__ __device__ inline size_t warp_scratch_bytes(uint32_t ef, uint32_t bloom_log2, uint32_t kept_rows) {
+    size_t list = ((size_t)ef * 8 + 15) & ~(size_t)15;
+    return list + ((size_t)1 << bloom_log2) / 8 + (size_t)kept_rows * 128 + kMaxWidth * 8 + 32 * 4;
+}
+
+__device__ __forceinline__ WarpScratch carve_scratch(unsigned char* base, uint32_t ef, uint32_t bloom_log2,
+                                                     uint32_t kept_rows) {
+    WarpScratch w;
+    size_t list = ((size_t)ef * 8 + 15) & ~(size_t)15;
+    w.kept = reinterpret_cast<uint4*>(base);
+    base += (size_t)kept_rows * 128;
+    w.list = reinterpret_cast<uint64_t*>(base);
+    base += list;
+    w.sel = reinterpret_cast<uint64_t*>(base);
+    base += kMaxWidth * 8;
+    w.bloom = reinterpret_cast<uint32_t*>(base);
+    base += ((size_t)1 << bloom_log2) / 8;
+    w.ids = reinterpret_cast<uint32_t*>(base);
+    w.bloom_log2 = bloom_log2;
+    return w;
+}
+
+// ------------------------------------------------------------------------------------------------ distances
+// Lane j < cnt holds ids_j; returns to lane j the order key bits of d(query, ids_j).  cnt is warp-uniform, <= 32.
+__device__ __forceinline__ uint32_t warp_eval(const uint4* __restrict__ fp, uint4 q4, uint32_t ids, uint32_t cnt) {
+    const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
+    uint32_t mine = 0;
+    for (uint32_t r0 = 0; r0 * 4 < cnt; r0 += 4) {
+        uint4 a[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            uint32_t j = (r0 + r) * 4 + grp;
+            uint32_t id = __shfl_sync(RB_FULL_MASK, ids, j & 31);
+            a[r] = (j < cnt) ? load_slice(fp, id, sub) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            uint32_t v = group8_inter_union(a[r], q4);
+            uint32_t bits = order_key_bits(v & 0xFFFFu, v >> 16);
+            uint32_t got = __shfl_sync(RB_FULL_MASK, bits, (lane & 3) * 8);
+            if ((uint32_t)(lane >> 2) == r0 + r)
+                mine = got;
+        }
+    }
+    return mine;
+}
+
+// distance of the query to ONE slot, result in every lane
+__device__ __forceinline__ uint32_t warp_eval_one(const uint4* __restrict__ fp, uint4 q4, uint32_t slot) {
+    uint4 a = load_slice(fp, slot, threadIdx.x & 7);
+    uint32_t v = group8_inter_union(a, q4);
+    return order_key_bits(v & 0xFFFFu, v >> 16);
+}
+
+// ------------------------------------------------------------------------------------------------ Bloom filter
+__device__ __forceinline__ void bloom_positions(uint32_t x, uint32_t log2bits, uint32_t h[3]) {
+    uint32_t a = x * 0x9E3779B1u, b = (x * 0x85EBCA77u) | 1u;
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+        h[j] = (a + (uint32_t)j * b) >> (32 - log2bits);
+}
+__device__ __forceinline__ bool bloom_test(const uint32_t* bl, uint32_t x, uint32_t log2bits) {
+    uint32_t h[3];
+    bloom_positions(x, log2bits, h);
+    return ((bl[h[0] >> 5] >> (h[0] & 31)) & (bl[h[1] >> 5] >> (h[1] & 31)) & (bl[h[2] >> 5] >> (h[2] & 31)) & 1u) != 0;
+}
+__device__ __forceinline__ void bloom_set(uint32_t* bl, uint32_t x, uint32_t log2bits) {
+    uint32_t h[3];
+    bloom_positions(x, log2bits, h);
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+        atomicOr(&bl[h[j] >> 5], 1u << (h[j] & 31));
+}
+
+// ------------------------------------------------------------------------------------------------ sorted list
+// Insert `key` (expanded bit clear) into the ascending list of at most `ef` keys held in shared memory.
+// Warp-uniform arguments; returns the insert position or 0xFFFFFFFF when the key does not qualify.
+__device__ __forceinline__ uint32_t list_insert(uint64_t* list, uint32_t& len, uint32_t ef, uint64_t key) {
+    const int lane = threadIdx.x & 31;
+    if (len == ef && key >= (list[ef - 1] & ~1ull))
+        return 0xFFFFFFFFu;
+    // position = number of entries smaller than key: coarse pass over 32 pivots, fine pass inside one segment
+    uint32_t step = (len + 31) >> 5;
+    uint32_t pos = 0;
+    if (len) {
+        uint32_t pidx = (uint32_t)lane * step;
+        bool below = pidx < len && (list[pidx] & ~1ull) < key;
+        uint32_t seg = __popc(__ballot_sync(RB_FULL_MASK, below));  // pivots 0..seg-1 are smaller
+        if (seg) {
+            uint32_t base = (seg - 1) * step;  // entries [0, base] are smaller; look inside (base, base + step)
+            uint32_t idx = base + 1 + lane;
+            bool below2 = (uint32_t)lane + 1 < step && idx < len && (list[idx] & ~1ull) < key;
+            pos = base + 1 + __popc(__ballot_sync(RB_FULL_MASK, below2));
+        }
+    }
+    uint32_t end = (len == ef) ? ef - 1 : len;  // entries [pos, end) move up by one
+    for (uint32_t hi = end; hi > pos;) {
+        uint32_t lo = (hi - pos > 32) ? hi - 32 : pos;
+        uint32_t idx = lo + lane;
+        uint64_t v = 0;
+        bool act = idx < hi;
+        if (act)
+            v = list[idx];
+        __syncwarp();
+        if (act)
+            list[idx + 1] = v;
+        __syncwarp();
+        hi = lo;
+    }
+    if (lane == 0)
+        list[pos] = key;
+    __syncwarp();
+    if (len < ef)
+        ++len;
+    return pos;
+}
+
+struct TraversalCounters {
+    uint32_t distances;
+    uint32_t expansions;
+};
+
+// ------------------------------------------------------------------------------------------------ greedy descent
+// index.hpp:3935-3975: move to the best neighbour until no neighbour improves, on levels (from, to].
+__device__ __forceinline__ void warp_greedy_descent(const GraphView& g, uint4 q4, uint32_t& cur, uint32_t& cur_bits,
+                                                    int from_level, int to_level, TraversalCounters& tc) {
+    const int lane = threadIdx.x & 31;
+    for (int level = from_level; level > to_level; --level) {
+        bool changed;
+        do {
+            changed = false;
+            uint32_t width;
+            const uint32_t* row = graph_row(g, cur, level, width);
+            uint32_t nid = (uint32_t)lane < width ? __ldg(row + lane) : RB_EMPTY;
+            uint32_t cnt = __popc(__ballot_sync(RB_FULL_MASK, nid != RB_EMPTY));  // rows are packed at the front
+            uint32_t bits = warp_eval(g.fp, q4, nid, cnt);
+            tc.distances += cnt;
+            tc.expansions += 1;
+            // first strict improvement in list order wins ties exactly like the sequential scan: min over (bits, lane)
+            uint64_t mine = (uint32_t)lane < cnt ? (((uint64_t)bits << 32) | (uint32_t)lane) : ~0ull;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                uint64_t other = __shfl_xor_sync(RB_FULL_MASK, mine, o);
+                mine = other < mine ? other : mine;
+            }
+            uint32_t best_bits = (uint32_t)(mine >> 32);
+            if (mine != ~0ull && best_bits < cur_bits) {
+                cur = __shfl_sync(RB_FULL_MASK, nid, (int)(mine & 31));
+                cur_bits = best_bits;
+                changed = true;
+            }
+        } while (changed);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ beam search
+// ef-bounded best-first search on one level.  Leaves the ascending candidate list in w.list and returns its length.
+__device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const WarpScratch& w, uint4 q4, uint32_t start,
+                                                     uint32_t start_bits, int level, uint32_t ef,
+                                                     TraversalCounters& tc) {
+    const int lane = threadIdx.x & 31;
+    // clear the filter
+    {
+        uint4* b4 = reinterpret_cast<uint4*>(w.bloom);
+        uint32_t n4 = (1u << w.bloom_log2) / 128;
+        for (uint32_t i = lane; i < n4; i += 32)
+            b4[i] = make_uint4(0, 0, 0, 0);
+    }
+    __syncwarp();
+    uint32_t len = 0;
+    if (lane == 0) {
+        w.list[0] = make_key(start_bits, start);
+        bloom_set(w.bloom, start, w.bloom_log2);
+    }
+    len = 1;
+    __syncwarp();
+    uint32_t hint = 0;  // every entry before `hint` is expanded
+    for (;;) {
+        // first unexpanded entry
+        uint32_t pos = 0xFFFFFFFFu;
+        for (uint32_t base = hint; base < len; base += 32) {
+            uint32_t idx = base + lane;
+            bool open = idx < len && !(w.list[idx] & 1ull);
+            uint32_t mask = __ballot_sync(RB_FULL_MASK, open);
+            if (mask) {
+                pos = base + (uint32_t)__ffs((int)mask) - 1;
+                break;
+            }
+        }
+        if (pos == 0xFFFFFFFFu)
+            break;
+        uint64_t cur_key = w.list[pos];
+        __syncwarp();
+        if (lane == 0)
+            w.list[pos] = cur_key | 1ull;
+        hint = pos + 1;
+        tc.expansions += 1;
+        uint32_t v = key_slot(cur_key);
+        uint32_t width;
+        const uint32_t* row = graph_row(g, v, level, width);
+        uint32_t nid = (uint32_t)lane < width ? __ldg(row + lane) : RB_EMPTY;
+        bool fresh = nid != RB_EMPTY && !bloom_test(w.bloom, nid, w.bloom_log2);
+        __syncwarp();  // every lane has tested against the state before this expansion
+        if (fresh)
+            bloom_set(w.bloom, nid, w.bloom_log2);
+        uint32_t mask = __ballot_sync(RB_FULL_MASK, fresh);
+        uint32_t cnt = __popc(mask);
+        if (!cnt)
+            continue;
+        if (fresh)
+            w.ids[__popc(mask & ((1u << lane) - 1u))] = nid;
+        __syncwarp();
+        uint32_t id = (uint32_t)lane < cnt ? w.ids[lane] : 0u;
+        __syncwarp();
+        uint32_t bits = warp_eval(g.fp, q4, id, cnt);
+        tc.distances += cnt;
+        uint64_t key = make_key(bits, id);
+        uint64_t worst = (len == ef) ? (w.list[ef - 1] & ~1ull) : ~0ull;
+        uint32_t acc = __ballot_sync(RB_FULL_MASK, (uint32_t)lane < cnt && key < worst);
+        while (acc) {
+            int j = __ffs((int)acc) - 1;
+            acc &= acc - 1;
+            uint64_t k = __shfl_sync(RB_FULL_MASK, key, j);
+            uint32_t at = list_insert(w.list, len, ef, k);
+            if (at < hint)
+                hint = at;
+        }
+    }
+    return len;
+}
+
+// ------------------------------------------------------------------------------------------------ selection heuristic
+// index.hpp:4246-4289 over `count` ascending keys in shared memory `cand`; writes the selected keys to w.sel and
+// returns how many (<= needed <= kMaxWidth).  Keys keep their low (expanded) bit; callers mask it.
+__device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, const WarpScratch& w, const uint64_t* cand,
+                                                          uint32_t count, uint32_t needed, TraversalCounters& tc) {
+    const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
+    if (count < needed) {
+        for (uint32_t i = lane; i < count; i += 32)
+            w.sel[i] = cand[i];
+        __syncwarp();
+        return count;
+    }
+    // the closest candidate is always kept
+    {
+        uint64_t k0 = cand[0];
+        if (lane < 8)
+            w.kept[sub] = load_slice(g.fp, key_slot(k0), sub);
+        if (lane == 0)
+            w.sel[0] = k0;
+    }
+    __syncwarp();
+    uint32_t kept = 1, c = 1;
+    while (kept < needed && c < count) {
+        uint32_t ci = c + grp;  // each group of 8 lanes examines one candidate
+        bool have = ci < count;
+        uint64_t ck = have ? cand[ci] : 0ull;
+        uint32_t cbits = key_bits(ck);
+        uint4 a = have ? load_slice(g.fp, key_slot(ck), sub) : make_uint4(0, 0, 0, 0);
+        bool good = have;
+        for (uint32_t j = 0; j < kept; ++j) {
+            uint4 s = w.kept[j * 8 + sub];
+            uint32_t v = group8_inter_union(a, s);
+            uint32_t between = order_key_bits(v & 0xFFFFu, v >> 16);
+            good = good && !(between < cbits);
+        }
+        tc.distances += kept * (count - c < 4 ? count - c : 4);
+        uint32_t gm = __ballot_sync(RB_FULL_MASK, good && sub == 0);  // bit 8*grp set when that candidate passes
+        if (!gm) {
+            c += 4;
+            continue;
+        }
+        int first = (__ffs((int)gm) - 1) >> 3;
+        if (grp == first) {
+            w.kept[kept * 8 + sub] = a;
+            if (sub == 0)
+                w.sel[kept] = ck;
+        }
+        __syncwarp();
+        ++kept;
+        c += (uint32_t)first + 1;
+    }
+    return kept;
+}
+
+// ------------------------------------------------------------------------------------------------ insertion
+struct InsertParams {
+    GraphView g;
+    const int8_t* levels;      // per slot
+    const uint32_t* task_rel;  // per slot: first task of the node, relative to its batch
+    uint64_t* pair_keys;       // [tasks x m]  level << 32 | target      (~0 = unused)
+    uint64_t* pair_vals;       // [tasks x m]  order bits << 32 | source
+    uint32_t batch_start, batch_size;
+    uint32_t entry;
+    int32_t max_level;
+    uint32_t ef;
+    uint32_t bloom_log2;
+    unsigned int* work_counter;
+    unsigned long long* counters;  // [0] distances, [1] expansions
+};
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) insert_kernel(InsertParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
+    WarpScratch w = carve_scratch(smem + (size_t)warp * warp_scratch_bytes(p.ef, p.bloom_log2, p.g.m), p.ef,
+                                  p.bloom_log2, p.g.m);
+    TraversalCounters tc{0, 0};
+    for (;;) {
+        uint32_t t = 0;
+        if (lane == 0)
+            t = atomicAdd(p.work_counter, 1u);
+        t = __shfl_sync(RB_FULL_MASK, t, 0);
+        if (t >= p.batch_size)
+            break;
+        const uint32_t slot = p.batch_start + t;
+        const uint4 q4 = load_slice(p.g.fp, slot, sub);
+        const int lq = p.levels[slot];
+        uint32_t cur = p.entry;
+        uint32_t cur_bits = warp_eval_one(p.g.fp, q4, cur);
+        tc.distances += 1;
+        warp_greedy_descent(p.g, q4, cur, cur_bits, p.max_level, lq, tc);
+        uint32_t task = p.task_rel[slot];
+        for (int level = lq < p.max_level ? lq : p.max_level; level >= 0; --level, ++task) {
+            uint32_t len = warp_beam_search(p.g, w, q4, cur, cur_bits, level, p.ef, tc);
+            uint32_t ns = warp_select_neighbors(p.g, w, w.list, len, p.g.m, tc);
+            uint32_t width;
+            uint32_t* mine = graph_row(p.g, slot, level, width);
+            uint64_t sk = (uint32_t)lane < ns ? w.sel[lane] : 0ull;
+            if ((uint32_t)lane < width)
+                mine[lane] = (uint32_t)lane < ns ? key_slot(sk) : RB_EMPTY;
+            if ((uint32_t)lane < p.g.m) {
+                size_t at = (size_t)task * p.g.m + lane;
+                bool on = (uint32_t)lane < ns;
+                p.pair_keys[at] = on ? (((uint64_t)(uint32_t)level << 32) | key_slot(sk)) : ~0ull;
+                p.pair_vals[at] = on ? (((uint64_t)key_bits(sk) << 32) | slot) : 0ull;
+            }
+            uint64_t k0 = w.list[0];
+            cur = key_slot(k0);
+            cur_bits = key_bits(k0);
+            __syncwarp();
+        }
+    }
+    if (lane == 0) {
+        atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+        atomicAdd(p.counters + 1, (unsigned long long)tc.expansions);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ reverse links
+struct ReverseParams {
+    GraphView g;
+    const uint64_t* pair_keys;  // sorted ascending; ~0 padding at the end
+    const uint64_t* pair_vals;
+    uint32_t pair_count;
+    unsigned long long* counters;
+};
+
+// bitonic sort of 64 keys held two per lane (a: index lane, b: index lane + 32), ascending
+__device__ __forceinline__ void warp_sort64(uint64_t& a, uint64_t& b) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int k = 2; k <= 64; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j == 32) {
+                // partner of index i is i ^ 32: a <-> b of the same lane; k == 64 -> ascending everywhere
+                uint64_t lo = a < b ? a : b, hi = a < b ? b : a;
+                a = lo;
+                b = hi;
+            } else {
+                uint64_t pa = __shfl_xor_sync(RB_FULL_MASK, a, j);
+                uint64_t pb = __shfl_xor_sync(RB_FULL_MASK, b, j);
+                bool upper = (lane & j) != 0;
+                bool asc_a = ((lane & k) == 0) || k == 64;         // index = lane
+                bool asc_b = (((lane + 32) & k) == 0) || k == 64;  // index = lane + 32
+                bool take_min_a = (asc_a != upper);
+                bool take_min_b = (asc_b != upper);
+                a = take_min_a ? (a < pa ? a : pa) : (a < pa ? pa : a);
+                b = take_min_b ? (b < pb ? b : pb) : (b < pb ? pb : b);
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(ReverseParams p) {
+    __shared__ __align__(16) unsigned char smem[kWarpsPerBlock * (kMaxWidth * 128 + kMaxWidth * 8 + kCandMax * 8 +
+                                                                   kIncomingCap * 8)];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
+    unsigned char* base = smem + (size_t)warp * (kMaxWidth * 128 + kMaxWidth * 8 + kCandMax * 8 + kIncomingCap * 8);
+    WarpScratch w;
+    w.kept = reinterpret_cast<uint4*>(base);
+    w.sel = reinterpret_cast<uint64_t*>(base + kMaxWidth * 128);
+    uint64_t* cand = reinterpret_cast<uint64_t*>(base + kMaxWidth * 128 + kMaxWidth * 8);
+    uint64_t* inc = cand + kCandMax;
+    w.list = nullptr;
+    w.bloom = nullptr;
+    w.ids = nullptr;
+    w.bloom_log2 = 0;
+
+    const uint32_t i = blockIdx.x * kWarpsPerBlock + warp;
+    if (i >= p.pair_count)
+        return;
+    const uint64_t key = p.pair_keys[i];
+    if (key == ~0ull || (i > 0 && p.pair_keys[i - 1] == key))
+        return;  // not the head of a (level, target) segment
+    const int level = (int)(key >> 32);
+    const uint32_t target = (uint32_t)key;
+    TraversalCounters tc{0, 0};
+
+    uint32_t width;
+    uint32_t* row = graph_row(p.g, target, level, width);
+    uint32_t have = (uint32_t)lane < width ? row[lane] : RB_EMPTY;
+    uint32_t deg = __popc(__ballot_sync(RB_FULL_MASK, have != RB_EMPTY));
+
+    // gather the incoming sources of this segment (source order), skipping anything already linked
+    uint32_t ni = 0;
+    for (uint32_t off = 0;; off += 32) {
+        uint32_t idx = i + off + lane;
+        bool in_seg = idx < p.pair_count && p.pair_keys[idx] == key;
+        uint32_t seg_mask = __ballot_sync(RB_FULL_MASK, in_seg);
+        uint64_t val = in_seg ? p.pair_vals[idx] : 0ull;
+        bool dup = false;
+        for (uint32_t e = 0; e < deg; ++e)
+            dup |= (__shfl_sync(RB_FULL_MASK, have, (int)e) == (uint32_t)val);
+        bool take = in_seg && !dup;
+        uint32_t tmask = __ballot_sync(RB_FULL_MASK, take);
+        uint32_t at = ni + __popc(tmask & ((1u << lane) - 1u));
+        if (take && at < kIncomingCap)
+            inc[at] = val;
+        ni += __popc(tmask);
+        if (seg_mask != RB_FULL_MASK)
+            break;  // the segment ended inside this chunk
+    }
+    if (ni > kIncomingCap)
+        ni = kIncomingCap;
+    __syncwarp();
+    if (!ni)
+        return;
+
+    if (deg + ni <= width) {
+        if ((uint32_t)lane < ni)
+            row[deg + lane] = (uint32_t)inc[lane];
+        return;
+    }
+
+    // saturated: re-prune existing + the closest incoming, at most kCandMax candidates in total
+    uint32_t room = kCandMax - deg;
+    if (ni > room) {
+        // keep the `room` smallest incoming keys (order bits << 32 | source): rank by counting, ni <= kIncomingCap
+        for (uint32_t base_i = 0; base_i < ni; base_i += 32) {
+            uint32_t idx = base_i + lane;
+            uint64_t mine = idx < ni ? inc[idx] : ~0ull;
+            uint32_t rank = 0;
+            for (uint32_t j = 0; j < ni; ++j)
+                rank += inc[j] < mine;
+            __syncwarp();
+            if (idx < ni && rank < room)
+                cand[deg + rank] = ((mine >> 32) << 32) | ((uint64_t)(uint32_t)mine << 1);
+        }
+        ni = room;
+    } else {
+        if ((uint32_t)lane < ni)
+            cand[deg + lane] = ((inc[lane] >> 32) << 32) | ((uint64_t)(uint32_t)inc[lane] << 1);
+        if ((uint32_t)lane + 32 < ni)
+            cand[deg + lane + 32] = ((inc[lane + 32] >> 32) << 32) | ((uint64_t)(uint32_t)inc[lane + 32] << 1);
+    }
+    // distances from the target to its current neighbours
+    {
+        uint4 t4 = load_slice(p.g.fp, target, sub);
+        uint32_t bits = warp_eval(p.g.fp, t4, have, deg);
+        tc.distances += deg;
+        if ((uint32_t)lane < deg)
+            cand[lane] = make_key(bits, have);
+    }
+    __syncwarp();
+    uint32_t nc = deg + ni;
+    uint64_t a = (uint32_t)lane < nc ? cand[lane] : ~0ull;
+    uint64_t b = (uint32_t)lane + 32 < nc ? cand[lane + 32] : ~0ull;
+    __syncwarp();
+    warp_sort64(a, b);
+    cand[lane] = a;
+    cand[lane + 32] = b;
+    __syncwarp();
+    uint32_t ns = warp_select_neighbors(p.g, w, cand, nc, width, tc);
+    if ((uint32_t)lane < width)
+        row[lane] = (uint32_t)lane < ns ? key_slot(w.sel[lane]) : RB_EMPTY;
+    if (lane == 0)
+        atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+}
+
+// ------------------------------------------------------------------------------------------------ approximate search
+struct SearchParams {
+    GraphView g;
+    const uint4* queries;  // Q x 8 uint4
+    uint32_t query_count;
+    uint32_t entry;
+    int32_t max_level;
+    uint32_t ef, k;
+    uint32_t bloom_log2;
+    uint32_t* slots_out;   // Q x k
+    float* dists_out;      // Q x k  (reference-exact bits)
+    int32_t* counts_out;   // Q
+    unsigned int* work_counter;
+    unsigned long long* counters;
+};
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) search_kernel(SearchParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
+    WarpScratch w = carve_scratch(smem + (size_t)warp * warp_scratch_bytes(p.ef, p.bloom_log2, p.g.m), p.ef,
+                                  p.bloom_log2, p.g.m);
+    TraversalCounters tc{0, 0};
+    for (;;) {
+        uint32_t qi = 0;
+        if (lane == 0)
+            qi = atomicAdd(p.work_counter, 1u);
+        qi = __shfl_sync(RB_FULL_MASK, qi, 0);
+        if (qi >= p.query_count)
+            break;
+        const uint4 q4 = __ldg(p.queries + (size_t)qi * 8 + sub);
+        uint32_t cur = p.entry;
+        uint32_t cur_bits = warp_eval_one(p.g.fp, q4, cur);
+        tc.distances += 1;
+        warp_greedy_descent(p.g, q4, cur, cur_bits, p.max_level, 0, tc);
+        uint32_t len = warp_beam_search(p.g, w, q4, cur, cur_bits, 0, p.ef, tc);
+        uint32_t cnt = len < p.k ? len : p.k;
+        // reference-exact distances for what is returned (the traversal ran on order keys)
+        for (uint32_t base = 0; base < cnt; base += 4) {
+            uint32_t j = base + (lane >> 3);
+            uint32_t id = j < cnt ? key_slot(w.list[j]) : 0u;
+            uint4 a = j < cnt ? load_slice(p.g.fp, id, sub) : make_uint4(0, 0, 0, 0);
+            uint32_t v = group8_inter_union(a, q4);
+            if (j < cnt && sub == 0) {
+                p.slots_out[(size_t)qi * p.k + j] = id;
+                p.dists_out[(size_t)qi * p.k + j] = __uint_as_float(exact_distance_bits(v & 0xFFFFu, v >> 16));
+            }
+        }
+        if (lane == 0)
+            p.counts_out[qi] = (int32_t)cnt;
+        __syncwarp();
+    }
+    if (lane == 0) {
+        atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+        atomicAdd(p.counters + 1, (unsigned long long)tc.expansions);
+    }
+}
+
+}  // namespace rb
