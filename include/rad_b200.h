@@ -35,6 +35,7 @@ typedef int (*rb_progress_t)(uint64_t processed, uint64_t total, void* user);
 
 enum {
     RB_FLAG_LAZY_HOST_SYNC = 1u, /* do not copy the graph back to the host after every rb_add; call rb_sync_host */
+    RB_FLAG_TIME_KERNELS = 2u,   /* CUDA events around every build kernel; fills rb_counters_t::*_ms (bench / roofline) */
 };
 
 /* usearch/python/lib.cpp:116-147 (make_index) / usearch/c/usearch.h:94-123 (usearch_init_options_t) */
@@ -73,6 +74,11 @@ typedef struct rb_counters {
     uint64_t batches;              /* insertion batches launched                                              */
     uint64_t kernel_launches;      /* CUDA kernels of this library launched                                   */
     double device_ms;              /* CUDA-event time of the device work, on the library's stream             */
+    /* with RB_FLAG_TIME_KERNELS: summed CUDA-event durations of each kernel class of the last rb_add */
+    double insert_ms;              /* insert_kernel (beam search + heuristic select + forward links)          */
+    double sort_ms;                /* radix sort of the (level, target) reverse pairs                         */
+    double reverse_ms;             /* reverse_link_kernel                                                     */
+    uint64_t insert_launches;      /* insert_kernel launches (= batches that did graph work)                  */
 } rb_counters_t;
 
 /* ---------------------------------------------------------------- lifetime: python/lib.cpp:116-147, index.py:1154-1162 */
@@ -92,6 +98,12 @@ RB_EXPORT void rb_add(rb_index_t* index, uint64_t const* keys, uint8_t const* ve
 RB_EXPORT void rb_add_device(rb_index_t* index, uint64_t const* keys, void const* d_vectors, size_t count,
                              rb_error_t* error);
 RB_EXPORT void rb_sync_host(rb_index_t* index, rb_error_t* error);
+/* Index.clear(): forget every node but keep the reserved host and device memory (index.py:1150-1152 ->
+ * index_dense.hpp:989-998 clear(): "erases all vectors from the index, preserving the allocated space") */
+RB_EXPORT void rb_clear(rb_index_t* index, rb_error_t* error);
+/* the cudaStream_t (as an integer) every kernel of this handle is launched on, so that callers can bracket calls
+ * with their own CUDA events; 0 until the first device call */
+RB_EXPORT uintptr_t rb_stream(rb_index_t const* index);
 
 /* ---------------------------------------------------------------- search: python/lib.cpp:511-557 (search_many_in_index),
  * index.hpp:2970-3029 (search), 4222-4239 (search_exact_: ties by descending slot, 923-934).

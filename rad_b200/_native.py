@@ -45,11 +45,13 @@ class Metadata(C.Structure):
 
 class Counters(C.Structure):
     _fields_ = [("computed_distances", C.c_uint64), ("visited_members", C.c_uint64), ("batches", C.c_uint64),
-                ("kernel_launches", C.c_uint64), ("device_ms", C.c_double)]
+                ("kernel_launches", C.c_uint64), ("device_ms", C.c_double), ("insert_ms", C.c_double),
+                ("sort_ms", C.c_double), ("reverse_ms", C.c_double), ("insert_launches", C.c_uint64)]
 
 
 PROGRESS = C.CFUNCTYPE(C.c_int, C.c_uint64, C.c_uint64, C.c_void_p)
 RB_FLAG_LAZY_HOST_SYNC = 1
+RB_FLAG_TIME_KERNELS = 2
 
 _ERR = C.POINTER(C.c_char_p)
 _H = C.c_void_p
@@ -65,6 +67,8 @@ SIGNATURES = {
     "rb_add": (None, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, PROGRESS, C.c_void_p, _ERR]),
     "rb_add_device": (None, [_H, C.c_void_p, C.c_void_p, C.c_size_t, _ERR]),
     "rb_sync_host": (None, [_H, _ERR]),
+    "rb_clear": (None, [_H, _ERR]),
+    "rb_stream": (C.c_size_t, [_H]),
     "rb_search": (None, [_H, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p,
                          C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), _ERR]),
     "rb_search_device": (None, [_H, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,

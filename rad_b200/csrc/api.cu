@@ -433,6 +433,16 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     bool cancelled = false;
     std::vector<cudaEvent_t> marks;  // progress marks
     size_t next_mark = 0;
+    const bool time_kernels = (ix->opts.flags & RB_FLAG_TIME_KERNELS) != 0;
+    std::vector<cudaEvent_t> ticks;  // 4 per batch with graph work: before insert, after insert, after sort, after reverse
+    auto tick = [&]() -> cudaError_t {
+        cudaEvent_t ev;
+        cudaError_t e = cudaEventCreate(&ev);
+        if (e != cudaSuccess)
+            return e;
+        ticks.push_back(ev);
+        return cudaEventRecord(ev, d.stream);
+    };
     RB_CUDA(cudaEventRecord(d.ev_begin, d.stream));
     for (size_t bi = 0; bi < batches.size(); ++bi) {
         Batch const& b = batches[bi];
@@ -453,7 +463,11 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
             ip.counters = d.counters;
             unsigned blocks = (unsigned)std::min<size_t>((b.size + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
                                                          (size_t)d.sm_count * d.insert_blocks_per_sm);
+            if (time_kernels)
+                RB_CUDA(tick());
             rb::insert_kernel<<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
+            if (time_kernels)
+                RB_CUDA(tick());
             const size_t pairs = (size_t)b.tasks * h.m;
             size_t tmp = d.sort_tmp_bytes;
             RB_CUDA(cub::DeviceRadixSort::SortPairs(d.sort_tmp, tmp, d.pair_keys[0], d.pair_keys[1], d.pair_vals[0],
@@ -465,7 +479,11 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
             rp.pair_count = (uint32_t)pairs;
             rp.counters = d.counters;
             unsigned rblocks = (unsigned)((pairs + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock);
+            if (time_kernels)
+                RB_CUDA(tick());
             rb::reverse_link_kernel<<<rblocks, rb::kWarpsPerBlock * 32, 0, d.stream>>>(rp);
+            if (time_kernels)
+                RB_CUDA(tick());
             launches += 2 + 4;  // ours + the radix-sort passes over 40 key bits (library code)
             RB_CUDA(cudaGetLastError());
         }
@@ -502,6 +520,20 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     ix->last.batches = batches.size();
     ix->last.kernel_launches = launches;
     ix->last.device_ms = ms;
+    ix->last.insert_ms = ix->last.sort_ms = ix->last.reverse_ms = 0;
+    ix->last.insert_launches = 0;
+    for (size_t t = 0; t + 3 < ticks.size(); t += 4) {
+        float a = 0, b2 = 0, c = 0;
+        cudaEventElapsedTime(&a, ticks[t], ticks[t + 1]);
+        cudaEventElapsedTime(&b2, ticks[t + 1], ticks[t + 2]);
+        cudaEventElapsedTime(&c, ticks[t + 2], ticks[t + 3]);
+        ix->last.insert_ms += a;
+        ix->last.sort_ms += b2;
+        ix->last.reverse_ms += c;
+        ix->last.insert_launches += 1;
+    }
+    for (cudaEvent_t ev : ticks)
+        cudaEventDestroy(ev);
 
     // commit what was inserted (everything unless a debug cap or a cancellation cut the schedule short)
     accepted = inserted;
@@ -901,6 +933,21 @@ void rb_add_device(rb_index_t* ix, uint64_t const* keys, void const* d_vectors, 
     if (!err.empty())
         RB_FAIL(err);
 }
+
+void rb_clear(rb_index_t* ix, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    const size_t capacity = ix->host.capacity;
+    ix->host.reset_graph();
+    ix->host.viewing = false;
+    ix->host.capacity = capacity;
+    ix->dev.rows = ix->dev.upper_rows = 0;
+    ix->device_graph_valid = ix->dev.device >= 0;  // an empty graph; the arrays keep their capacity
+    ix->host_graph_valid = true;
+    ix->last = rb_counters_t{};
+}
+
+uintptr_t rb_stream(rb_index_t const* ix) { return reinterpret_cast<uintptr_t>(ix->dev.stream); }
 
 void rb_sync_host(rb_index_t* ix, rb_error_t* error) {
     if (error)

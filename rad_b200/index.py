@@ -193,6 +193,7 @@ class Index:
         exclude_vectors: bool = False,
         device: int = -1,
         lazy_host_sync: bool = False,
+        time_kernels: bool = False,
         batch_growth_den: int = 0,
         batch_max: int = 0,
         bloom_bits_log2: int = 0,
@@ -218,7 +219,8 @@ class Index:
         opts = _native.InitOptions(
             dimensions=ndim, connectivity=connectivity, expansion_add=expansion_add,
             expansion_search=expansion_search, device=device,
-            flags=_native.RB_FLAG_LAZY_HOST_SYNC if lazy_host_sync else 0,
+            flags=(_native.RB_FLAG_LAZY_HOST_SYNC if lazy_host_sync else 0)
+            | (_native.RB_FLAG_TIME_KERNELS if time_kernels else 0),
             batch_growth_den=batch_growth_den, batch_max=batch_max, bloom_bits_log2=bloom_bits_log2,
             debug_max_batches=_debug_max_batches)
         err = C.c_char_p()
@@ -425,7 +427,10 @@ class Index:
         raise NotImplementedError("cluster() is outside RAD's path and not implemented by rad_b200")
 
     def clear(self):
-        raise NotImplementedError("clear() is outside RAD's path; construct a new Index instead")
+        """Erases all vectors from the index, preserving the allocated space (reference: index.py:1150-1152)."""
+        err = C.c_char_p()
+        self._lib.rb_clear(self._handle(), C.byref(err))
+        self._check(err)
 
     # ------------------------------------------------------------------ properties (index.py:895-1059, 1315-1386)
     @property
@@ -538,7 +543,9 @@ class Index:
         c = _native.Counters()
         self._lib.rb_last_counters(self._handle(), C.byref(c))
         return dict(computed_distances=int(c.computed_distances), visited_members=int(c.visited_members),
-                    batches=int(c.batches), kernel_launches=int(c.kernel_launches), device_ms=float(c.device_ms))
+                    batches=int(c.batches), kernel_launches=int(c.kernel_launches), device_ms=float(c.device_ms),
+                    insert_ms=float(c.insert_ms), sort_ms=float(c.sort_ms), reverse_ms=float(c.reverse_ms),
+                    insert_launches=int(c.insert_launches))
 
     def sync_host(self) -> None:
         err = C.c_char_p()
