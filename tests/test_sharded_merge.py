@@ -1,0 +1,74 @@
+"""Host-side logic of the N > 1 path (rad_b200/sharded.py) with world_size-2 gloo on CPU: shard bounds, the 64-bit key
+format (ascending key order == the reference's result order), the all-gather layout and the k-way merge rule
+(usearch index.hpp:2625-2645).  The per-shard top-k lists come from the oracle here (the checker); on the GPU the same
+keys are produced by rb_exact_topk_device and merged by rb_merge_topk_device (tests/test_gpu_exact.py)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import oracle as O
+from rad_b200 import sharded, synth
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_shard_bounds_cover_rows_exactly():
+    for n, w in [(10, 3), (7, 8), (100_000_000, 8), (1, 2), (0, 4)]:
+        spans = [sharded.shard_bounds(n, w, r) for r in range(w)]
+        assert spans[0][0] == 0 and spans[-1][1] == n
+        assert all(spans[i][1] == spans[i + 1][0] for i in range(w - 1))
+        sizes = [hi - lo for lo, hi in spans]
+        assert max(sizes) - min(sizes) <= 1
+
+
+def test_key_order_is_reference_order():
+    db = synth.clustered_fingerprints(3000, seed=31)
+    q = synth.queries_from_db(db, 40, seed=2)
+    slots, dists, counts = O.exact_search(db, q, 10)
+    keys = sharded.pack_topk_keys(dists, slots, counts)
+    assert (keys[:, 1:] > keys[:, :-1]).all()  # the oracle's order is strictly ascending in key space
+    s2, d2, c2 = sharded.unpack_topk_keys(keys)
+    assert np.array_equal(s2, slots.astype(np.uint64)) and np.array_equal(d2.view(np.uint32), dists.view(np.uint32))
+    assert np.array_equal(c2, counts)
+
+
+def _worker(rank, world, port, n, nq, k, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        db = synth.clustered_fingerprints(n, seed=17)
+        q = synth.heldout_queries(nq, seed=17, n_total=n)
+        lo, hi = sharded.shard_bounds(n, world, rank)
+        slots, dists, counts = O.exact_search(db[lo:hi], q, k)          # shard-local answers (local slots)
+        keys = sharded.pack_topk_keys(dists, slots.astype(np.uint64) + np.uint64(lo), counts)
+        part = torch.from_numpy(keys.view(np.int64).copy())
+        gathered = torch.empty((world, nq, k), dtype=torch.int64)
+        dist.all_gather_into_tensor(gathered.view(-1), part.view(-1))
+        merged = sharded.merge_topk_host(gathered.numpy(), k)
+        np.save(os.path.join(out_dir, f"merged_{rank}.npy"), merged)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,nq,k", [(2001, 33, 10), (5, 4, 10)])
+def test_two_rank_gather_and_merge_equals_unsharded(tmp_path, n, nq, k):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), n, nq, k, str(tmp_path)), nprocs=world, join=True)
+    db = synth.clustered_fingerprints(n, seed=17)
+    q = synth.heldout_queries(nq, seed=17, n_total=n)
+    slots, dists, counts = O.exact_search(db, q, k)
+    want = sharded.pack_topk_keys(dists, slots, counts)
+    a = np.load(tmp_path / "merged_0.npy")
+    b = np.load(tmp_path / "merged_1.npy")
+    assert np.array_equal(a, b)      # every rank holds the same merged answer
+    assert np.array_equal(a, want)   # and it is the unsharded reference answer, ties included
