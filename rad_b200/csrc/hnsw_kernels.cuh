@@ -64,28 +64,32 @@ __device__ __forceinline__ WarpScratch carve_scratch(unsigned char* base, uint32
 }
 
 // ------------------------------------------------------------------------------------------------ distances
-// Lane j < cnt holds ids_j; returns to lane j the order key bits of d(query, ids_j).  cnt is warp-uniform, <= 32.
-__device__ __forceinline__ uint32_t warp_eval(const uint4* __restrict__ fp, uint4 q4, uint32_t ids, uint32_t cnt) {
+// Lane j < cnt holds ids_j; returns to lane j the order key bits of d(query, ids_j).  cnt is warp-uniform, <= 4 * ROUNDS.
+// All ROUNDS loads of a lane are issued before the first is consumed: 4 * ROUNDS 128-byte lines in flight per warp.
+template <int ROUNDS>
+__device__ __forceinline__ uint32_t warp_eval_n(const uint4* __restrict__ fp, uint4 q4, uint32_t ids, uint32_t cnt) {
     const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
-    uint32_t mine = 0;
-    for (uint32_t r0 = 0; r0 * 4 < cnt; r0 += 4) {
-        uint4 a[4];
+    uint4 a[ROUNDS];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            uint32_t j = (r0 + r) * 4 + grp;
-            uint32_t id = __shfl_sync(RB_FULL_MASK, ids, j & 31);
-            a[r] = (j < cnt) ? load_slice(fp, id, sub) : make_uint4(0, 0, 0, 0);
-        }
-#pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            uint32_t v = group8_inter_union(a[r], q4);
-            uint32_t bits = order_key_bits(v & 0xFFFFu, v >> 16);
-            uint32_t got = __shfl_sync(RB_FULL_MASK, bits, (lane & 3) * 8);
-            if ((uint32_t)(lane >> 2) == r0 + r)
-                mine = got;
-        }
+    for (int r = 0; r < ROUNDS; ++r) {
+        uint32_t j = r * 4 + grp;
+        uint32_t id = __shfl_sync(RB_FULL_MASK, ids, j & 31);
+        a[r] = (j < cnt) ? load_slice(fp, id, sub) : make_uint4(0, 0, 0, 0);
     }
-    return mine;
+    uint32_t mine = 0;  // i | u << 16 of this lane's fingerprint
+#pragma unroll
+    for (int r = 0; r < ROUNDS; ++r) {
+        uint32_t v = group8_inter_union(a[r], q4);
+        uint32_t got = __shfl_sync(RB_FULL_MASK, v, (lane & 3) * 8);
+        if ((lane >> 2) == r)
+            mine = got;
+    }
+    // ONE divide per lane for up to 32 fingerprints (instead of one per group of four)
+    return order_key_bits(mine & 0xFFFFu, mine >> 16);
+}
+
+__device__ __forceinline__ uint32_t warp_eval(const uint4* __restrict__ fp, uint4 q4, uint32_t ids, uint32_t cnt) {
+    return cnt <= 16 ? warp_eval_n<4>(fp, q4, ids, cnt) : warp_eval_n<8>(fp, q4, ids, cnt);
 }
 
 // distance of the query to ONE slot, result in every lane
@@ -158,6 +162,88 @@ __device__ __forceinline__ uint32_t list_insert(uint64_t* list, uint32_t& len, u
     return pos;
 }
 
+// ascending bitonic sort of one u64 per lane; `top` = false skips the final 32-wide merge (valid when lanes 16..31
+// all hold ~0 and only the lower half matters)
+__device__ __forceinline__ uint64_t warp_sort32(uint64_t v, bool top) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+        if (k == 32 && !top)
+            break;
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            uint64_t o = __shfl_xor_sync(RB_FULL_MASK, v, j);
+            bool up = (lane & k) == 0 || k == 32;
+            bool lower = (lane & j) == 0;
+            uint64_t lo = v < o ? v : o, hi = v < o ? o : v;
+            v = (up == lower) ? lo : hi;
+        }
+    }
+    return v;
+}
+
+// Merge the candidates of one expansion (lane j holds `key` when `valid`; expanded bit clear) into the ascending
+// list in ONE pass: the result is exactly what inserting them one after the other with list_insert would leave
+// (the `ef` smallest of list + candidates; keys are unique because the visited filter has no false negatives).
+// Returns the smallest insert position, or 0xFFFFFFFF when nothing qualified.
+__device__ __forceinline__ uint32_t list_merge(uint64_t* list, uint32_t& len, uint32_t ef, uint64_t key, bool valid) {
+    const int lane = threadIdx.x & 31;
+    if (len == ef)
+        valid = valid && key < (list[ef - 1] & ~1ull);
+    const uint32_t mask = __ballot_sync(RB_FULL_MASK, valid);
+    if (!mask)
+        return 0xFFFFFFFFu;
+    const uint32_t cnt = __popc(mask);
+    if (cnt == 1) {
+        uint64_t k = __shfl_sync(RB_FULL_MASK, key, __ffs((int)mask) - 1);
+        return list_insert(list, len, ef, k);
+    }
+    // candidates ascending in lanes 0 .. cnt-1
+    uint64_t k = warp_sort32(valid ? key : ~0ull, (mask >> 16) != 0);
+    // lower bound of every candidate in the list: branch-free binary search, one per lane
+    uint32_t pos = 0;
+    if ((uint32_t)lane < cnt) {
+#pragma unroll
+        for (uint32_t step = 512; step; step >>= 1) {
+            uint32_t probe = pos + step;
+            if (probe <= len && (list[probe - 1] & ~1ull) < k)
+                pos = probe;
+        }
+    } else {
+        pos = 0xFFFFFFFFu;
+    }
+    const uint32_t pmin = __shfl_sync(RB_FULL_MASK, pos, 0);
+    // entries [pmin, len) move up by the number of candidates in front of them, highest chunk first
+    for (uint32_t hi = len; hi > pmin;) {
+        uint32_t lo = (hi - pmin > 32) ? hi - 32 : pmin;
+        uint32_t idx = lo + lane;
+        bool act = idx < hi;
+        uint64_t v = act ? list[idx] : 0ull;
+        uint32_t c = 0;  // number of candidates with pos <= idx (pos is ascending over lanes)
+#pragma unroll
+        for (uint32_t stp = 16; stp; stp >>= 1) {
+            uint32_t pv = __shfl_sync(RB_FULL_MASK, pos, (int)(c + stp - 1));
+            if (pv <= idx)
+                c += stp;
+        }
+        {
+            uint32_t pv = __shfl_sync(RB_FULL_MASK, pos, 31);
+            if (c == 31 && pv <= idx)
+                c = 32;
+        }
+        __syncwarp();
+        if (act && idx + c < ef)
+            list[idx + c] = v;
+        __syncwarp();
+        hi = lo;
+    }
+    if ((uint32_t)lane < cnt && pos + lane < ef)
+        list[pos + lane] = k;
+    __syncwarp();
+    len = (len + cnt < ef) ? len + cnt : ef;
+    return pmin;
+}
+
 struct TraversalCounters {
     uint32_t distances;
     uint32_t expansions;
@@ -218,32 +304,57 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
     len = 1;
     __syncwarp();
     uint32_t hint = 0;  // every entry before `hint` is expanded
+    // rows of at most 16 links are expanded TWO list entries at a time: lanes 0-15 read one row, lanes 16-31 the other
+    const uint32_t row_width = level == 0 ? g.m0 : g.m;
+    const bool two = row_width <= 16;
     for (;;) {
-        // first unexpanded entry
-        uint32_t pos = 0xFFFFFFFFu;
+        // first (two) unexpanded entries
+        uint32_t pos1 = 0xFFFFFFFFu, pos2 = 0xFFFFFFFFu;
         for (uint32_t base = hint; base < len; base += 32) {
             uint32_t idx = base + lane;
             bool open = idx < len && !(w.list[idx] & 1ull);
             uint32_t mask = __ballot_sync(RB_FULL_MASK, open);
             if (mask) {
-                pos = base + (uint32_t)__ffs((int)mask) - 1;
-                break;
+                if (pos1 == 0xFFFFFFFFu) {
+                    pos1 = base + (uint32_t)__ffs((int)mask) - 1;
+                    mask &= mask - 1;
+                }
+                if (two && mask)
+                    pos2 = base + (uint32_t)__ffs((int)mask) - 1;
+                if (!two || pos2 != 0xFFFFFFFFu)
+                    break;
             }
         }
-        if (pos == 0xFFFFFFFFu)
+        if (pos1 == 0xFFFFFFFFu)
             break;
-        uint64_t cur_key = w.list[pos];
+        const bool both = pos2 != 0xFFFFFFFFu;
+        uint64_t key1 = w.list[pos1];
+        uint64_t key2 = both ? w.list[pos2] : 0ull;
         __syncwarp();
-        if (lane == 0)
-            w.list[pos] = cur_key | 1ull;
-        hint = pos + 1;
-        tc.expansions += 1;
-        uint32_t v = key_slot(cur_key);
-        uint32_t width;
-        const uint32_t* row = graph_row(g, v, level, width);
-        uint32_t nid = (uint32_t)lane < width ? __ldg(row + lane) : RB_EMPTY;
+        if (lane == 0) {
+            w.list[pos1] = key1 | 1ull;
+            if (both)
+                w.list[pos2] = key2 | 1ull;
+        }
+        hint = (both ? pos2 : pos1) + 1;
+        tc.expansions += both ? 2 : 1;
+        uint32_t nid = RB_EMPTY;
+        {
+            const bool upper_half = two && lane >= 16;
+            const uint32_t col = two ? (uint32_t)(lane & 15) : (uint32_t)lane;
+            if (col < row_width && (!upper_half || both)) {
+                uint32_t width;
+                const uint32_t* row = graph_row(g, key_slot(upper_half ? key2 : key1), level, width);
+                nid = __ldg(row + col);
+            }
+        }
         bool fresh = nid != RB_EMPTY && !bloom_test(w.bloom, nid, w.bloom_log2);
-        __syncwarp();  // every lane has tested against the state before this expansion
+        if (both) {
+            // a neighbour listed in both rows is taken once (the lowest lane holding it)
+            uint32_t same = __match_any_sync(RB_FULL_MASK, nid);
+            fresh = fresh && (uint32_t)(__ffs((int)same) - 1) == (uint32_t)lane;
+        }
+        __syncwarp();  // every lane has tested against the state before this iteration
         if (fresh)
             bloom_set(w.bloom, nid, w.bloom_log2);
         uint32_t mask = __ballot_sync(RB_FULL_MASK, fresh);
@@ -257,17 +368,9 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         __syncwarp();
         uint32_t bits = warp_eval(g.fp, q4, id, cnt);
         tc.distances += cnt;
-        uint64_t key = make_key(bits, id);
-        uint64_t worst = (len == ef) ? (w.list[ef - 1] & ~1ull) : ~0ull;
-        uint32_t acc = __ballot_sync(RB_FULL_MASK, (uint32_t)lane < cnt && key < worst);
-        while (acc) {
-            int j = __ffs((int)acc) - 1;
-            acc &= acc - 1;
-            uint64_t k = __shfl_sync(RB_FULL_MASK, key, j);
-            uint32_t at = list_insert(w.list, len, ef, k);
-            if (at < hint)
-                hint = at;
-        }
+        uint32_t at = list_merge(w.list, len, ef, make_key(bits, id), (uint32_t)lane < cnt);
+        if (at < hint)
+            hint = at;
     }
     return len;
 }
@@ -342,7 +445,7 @@ struct InsertParams {
     unsigned long long* counters;  // [0] distances, [1] expansions
 };
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) insert_kernel(InsertParams p) {
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) insert_kernel(InsertParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
     WarpScratch w = carve_scratch(smem + (size_t)warp * warp_scratch_bytes(p.ef, p.bloom_log2, p.g.m), p.ef,
@@ -547,7 +650,7 @@ struct SearchParams {
     unsigned long long* counters;
 };
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) search_kernel(SearchParams p) {
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) search_kernel(SearchParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
     WarpScratch w = carve_scratch(smem + (size_t)warp * warp_scratch_bytes(p.ef, p.bloom_log2, p.g.m), p.ef,

@@ -14,8 +14,9 @@
  *   search    : per node, greedy descent on the levels above its own (index.hpp:3935-3975), then on each level
  *               l = min(level, max_level) .. 0 an ef-bounded best-first search with ONE sorted candidate list
  *               (key = f32 distance bits << 32 | slot), an "expanded" flag per entry and a Bloom filter
- *               (bloom_bits, 3 probes) as the visited set.  All neighbours of the expanded node are tested against
- *               the filter state BEFORE any of them is added.
+ *               (bloom_bits, 3 probes) as the visited set.  Each iteration expands the first TWO unexpanded entries
+ *               together when rows hold at most 16 links (one otherwise); all their neighbours are tested against
+ *               the filter state BEFORE any of them is added, duplicates between the two rows taken once.
  *   select    : the reference's heuristic (index.hpp:4246-4289) over the sorted list, needed = M.
  *   reverse   : per (level, target) the incoming sources of the whole batch are merged at once: appended in source
  *               order while the list has room, otherwise existing + incoming (closest 64 - deg by (distance, slot))
@@ -175,21 +176,35 @@ static void beam_search(const bm_index* ix, scratch_t* sc, const uint8_t* q, uin
     sc->len = 0;
     list_insert(sc, ef, ((uint64_t)start_bits << 32) | start);
     bloom_set(sc->bloom, start, ix->bloom_bits_log2);
+    /* rows of at most 16 links are expanded TWO list entries at a time (one warp reads both rows with one load) */
+    const uint32_t row_width = level == 0 ? ix->m0 : ix->m;
+    const uint32_t per_iter = row_width <= 16 ? 2 : 1;
     for (;;) {
-        uint32_t p = 0;
-        while (p < sc->len && sc->expanded[p])
-            ++p;
-        if (p == sc->len)
+        uint32_t open[2], no = 0;
+        for (uint32_t p = 0; p < sc->len && no < per_iter; ++p)
+            if (!sc->expanded[p])
+                open[no++] = p;
+        if (!no)
             break;
-        sc->expanded[p] = 1;
-        sc->expansions++;
-        uint32_t v = (uint32_t)sc->list[p];
-        uint32_t width;
-        const uint32_t* row = row_of(ix, v, level, &width);
         uint32_t fresh[64], nf = 0;
-        for (uint32_t j = 0; j < width && row[j] != EMPTY; ++j)
-            if (!bloom_test(sc->bloom, row[j], ix->bloom_bits_log2))
-                fresh[nf++] = row[j];
+        for (uint32_t e = 0; e < no; ++e) {
+            sc->expanded[open[e]] = 1;
+            sc->expansions++;
+            uint32_t v = (uint32_t)sc->list[open[e]];
+            uint32_t width;
+            const uint32_t* row = row_of(ix, v, level, &width);
+            /* every neighbour is tested against the filter state BEFORE this iteration; a neighbour that appears in
+             * both rows is taken once */
+            for (uint32_t j = 0; j < width && row[j] != EMPTY; ++j) {
+                if (bloom_test(sc->bloom, row[j], ix->bloom_bits_log2))
+                    continue;
+                int dup = 0;
+                for (uint32_t t = 0; t < nf; ++t)
+                    dup |= (fresh[t] == row[j]);
+                if (!dup)
+                    fresh[nf++] = row[j];
+            }
+        }
         for (uint32_t j = 0; j < nf; ++j)
             bloom_set(sc->bloom, fresh[j], ix->bloom_bits_log2);
         for (uint32_t j = 0; j < nf; ++j) {
