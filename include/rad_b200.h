@@ -48,7 +48,7 @@ typedef struct rb_init_options {
     uint32_t flags;            /* RB_FLAG_*                                                                   */
     uint32_t batch_growth_den; /* a batch holds at most size/den nodes; 0 -> 8                                */
     uint32_t batch_max;        /* upper bound of a batch; 0 -> 65536                                          */
-    uint32_t bloom_bits_log2;  /* visited filter size per traversal (bits, log2); 0 -> 16                     */
+    uint32_t bloom_bits_log2;  /* visited filter size per traversal (bits, log2); 0 -> 15                     */
     uint32_t debug_max_batches;/* stop an rb_add after this many batches (0 = unlimited); tests only          */
 } rb_init_options_t;
 

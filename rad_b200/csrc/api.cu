@@ -81,6 +81,7 @@ struct DeviceState {
     unsigned long long* counters = nullptr;  // [0] distances [1] expansions
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     int insert_blocks_per_sm = 0, search_blocks_per_sm = 0;
+    int insert_variant = 4, search_variant = 4;
     uint32_t insert_cfg_ef = 0, search_cfg_ef = 0;
     void* scratch = nullptr;  // grow-only arena for query / result staging
     size_t scratch_bytes = 0;
@@ -324,14 +325,31 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
     }
 }
 
+// resident CTAs per SM that `smem` bytes of dynamic shared memory per CTA allow, quantised to the compiled variants
+int traversal_variant(size_t smem) {
+    const size_t per_sm = 227 * 1024;
+    size_t fit = per_sm / (smem + 1024);  // 1 KB of system-reserved shared memory per CTA
+    return fit >= 8 ? 8 : fit >= 6 ? 6 : 4;
+}
+
+template <typename K4, typename K6, typename K8>
+std::string configure_variant(int variant, K4 k4, K6 k6, K8 k8, size_t smem, int& blocks_per_sm) {
+    const void* fn = variant == 8 ? (const void*)k8 : variant == 6 ? (const void*)k6 : (const void*)k4;
+    RB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    RB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fn, rb::kWarpsPerBlock * 32, smem));
+    return {};
+}
+
 std::string configure_traversal_kernels(rb_index* ix) {
     DeviceState& d = ix->dev;
     const uint32_t bloom = ix->opts.bloom_bits_log2, m = ix->host.m;
     if (d.insert_cfg_ef != ix->host.ef_add) {
         size_t smem = rb::warp_scratch_bytes(ix->host.ef_add, bloom, m) * rb::kWarpsPerBlock;
-        RB_CUDA(cudaFuncSetAttribute(rb::insert_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        RB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.insert_blocks_per_sm, rb::insert_kernel,
-                                                              rb::kWarpsPerBlock * 32, smem));
+        d.insert_variant = traversal_variant(smem);
+        std::string err = configure_variant(d.insert_variant, rb::insert_kernel<4>, rb::insert_kernel<6>,
+                                            rb::insert_kernel<8>, smem, d.insert_blocks_per_sm);
+        if (!err.empty())
+            return err;
         if (d.insert_blocks_per_sm < 1)
             return "expansion_add does not fit the shared memory of one SM";
         d.insert_cfg_ef = ix->host.ef_add;
@@ -343,9 +361,11 @@ std::string configure_search_kernel(rb_index* ix, uint32_t ef) {
     DeviceState& d = ix->dev;
     if (d.search_cfg_ef != ef) {
         size_t smem = rb::warp_scratch_bytes(ef, ix->opts.bloom_bits_log2, ix->host.m) * rb::kWarpsPerBlock;
-        RB_CUDA(cudaFuncSetAttribute(rb::search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        RB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.search_blocks_per_sm, rb::search_kernel,
-                                                              rb::kWarpsPerBlock * 32, smem));
+        d.search_variant = traversal_variant(smem);
+        std::string err = configure_variant(d.search_variant, rb::search_kernel<4>, rb::search_kernel<6>,
+                                            rb::search_kernel<8>, smem, d.search_blocks_per_sm);
+        if (!err.empty())
+            return err;
         if (d.search_blocks_per_sm < 1)
             return "expansion_search does not fit the shared memory of one SM";
         d.search_cfg_ef = ef;
@@ -465,7 +485,12 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
                                                          (size_t)d.sm_count * d.insert_blocks_per_sm);
             if (time_kernels)
                 RB_CUDA(tick());
-            rb::insert_kernel<<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
+            if (d.insert_variant == 8)
+                rb::insert_kernel<8><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
+            else if (d.insert_variant == 6)
+                rb::insert_kernel<6><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
+            else
+                rb::insert_kernel<4><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
             if (time_kernels)
                 RB_CUDA(tick());
             const size_t pairs = (size_t)b.tasks * h.m;
@@ -768,7 +793,12 @@ std::string search_on_device(rb_index* ix, uint4 const* d_queries, size_t nq, si
         size_t smem = rb::warp_scratch_bytes(ef, ix->opts.bloom_bits_log2, h.m) * rb::kWarpsPerBlock;
         unsigned blocks = (unsigned)std::min<size_t>((nq + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
                                                      (size_t)d.sm_count * d.search_blocks_per_sm);
-        rb::search_kernel<<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
+        if (d.search_variant == 8)
+            rb::search_kernel<8><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
+        else if (d.search_variant == 6)
+            rb::search_kernel<6><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
+        else
+            rb::search_kernel<4><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
         launches = 1;
     }
     RB_CUDA(cudaGetLastError());
@@ -856,7 +886,7 @@ rb_index_t* rb_init(rb_init_options_t const* options, rb_error_t* error) {
     if (!o.batch_max)
         o.batch_max = 65536;
     if (!o.bloom_bits_log2)
-        o.bloom_bits_log2 = 16;
+        o.bloom_bits_log2 = 15;
     if (o.bloom_bits_log2 < 10 || o.bloom_bits_log2 > 18) {
         set_error(error, "bloom_bits_log2 must be in 10..18");
         return nullptr;

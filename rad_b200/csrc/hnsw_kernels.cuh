@@ -445,7 +445,10 @@ struct InsertParams {
     unsigned long long* counters;  // [0] distances, [1] expansions
 };
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) insert_kernel(InsertParams p) {
+// MINB = resident CTAs per SM the register budget is sized for: 4 (<= 128 registers, 8 loads in flight per lane) when
+// shared memory allows no more, 6 or 8 when the per-warp scratch is small enough to fit them
+template <int MINB>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_kernel(InsertParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
     WarpScratch w = carve_scratch(smem + (size_t)warp * warp_scratch_bytes(p.ef, p.bloom_log2, p.g.m), p.ef,
@@ -650,7 +653,8 @@ struct SearchParams {
     unsigned long long* counters;
 };
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4) search_kernel(SearchParams p) {
+template <int MINB>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) search_kernel(SearchParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
     WarpScratch w = carve_scratch(smem + (size_t)warp * warp_scratch_bytes(p.ef, p.bloom_log2, p.g.m), p.ef,

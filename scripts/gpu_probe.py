@@ -1,6 +1,7 @@
 #!/usr/bin/env python3
 """Exploratory timings on the GPU box (not the bench): build and search throughput at a few sizes."""
 import ctypes as C
+import os
 import sys
 import time
 
@@ -54,7 +55,8 @@ for n in sizes:
         ms, _ = exact(d_db, d_q)
         print(f"exact  n={n} q={nq}: {ms:.2f} ms  {n * nq / ms / 1e6:.1f} G pairs/s", flush=True)
     for ef_add in (400,):
-        ix = Index(ndim=1024, connectivity=8, expansion_add=ef_add, expansion_search=64, lazy_host_sync=True)
+        ix = Index(ndim=1024, connectivity=8, expansion_add=ef_add, expansion_search=64, lazy_host_sync=True,
+                   bloom_bits_log2=int(os.environ.get("RB_BLOOM", "0")))
         t = time.perf_counter()
         L.rb_add_device(ix._handle(), None, d_db.data_ptr(), n, C.byref(err))
         _native.check(err)

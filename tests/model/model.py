@@ -45,7 +45,7 @@ def lib() -> C.CDLL:
 
 class BatchedModel:
     def __init__(self, vecs: np.ndarray, levels: np.ndarray, *, connectivity=8, expansion_add=400,
-                 bloom_bits_log2=16, growth_den=8, batch_max=65536):
+                 bloom_bits_log2=15, growth_den=8, batch_max=65536):
         self.vecs = np.ascontiguousarray(vecs, dtype=np.uint8)
         assert self.vecs.shape[1] == 128
         self.levels = np.ascontiguousarray(levels, dtype=np.int16)
