@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -18,6 +19,7 @@
 
 #include "../../include/rad_b200.h"
 #include "exact_kernels.cuh"
+#include "exact_i8_kernels.cuh"
 #include "hnsw_kernels.cuh"
 #include "host_index.hpp"
 #include "synth_kernels.cuh"
@@ -657,19 +659,37 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
 namespace {
 
 struct ExactPlan {
+    bool tensor;  // tcgen05 int8 kernel (128-query tiles, 256-row stages) instead of the POPC kernel (64 x 64)
     uint32_t chunks;
     uint64_t chunk_rows;
     size_t keys_bytes, iu_bytes;
 };
 
+// RB_EXACT_KERNEL=popc|i8 forces one of the two bit-identical kernels (tests, profiling)
+int exact_kernel_override() {
+    static int mode = [] {
+        char const* e = std::getenv("RB_EXACT_KERNEL");
+        if (!e)
+            return 0;
+        return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : 0;
+    }();
+    return mode;
+}
+
 ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     ExactPlan p;
-    uint64_t qtiles = std::max<uint64_t>(1, (nq + rb::kXQ - 1) / rb::kXQ);
-    uint64_t row_tiles = std::max<uint64_t>(1, (rows + rb::kXD - 1) / rb::kXD);
-    uint64_t want = std::max<uint64_t>(1, (1184 + qtiles - 1) / qtiles);  // about 4 waves of 148 x 2 CTAs
+    const int forced = exact_kernel_override();
+    // the tensor-core tile is 128 queries wide: worth it once at least half a tile is used and there is enough
+    // database to amortise unpacking the queries
+    p.tensor = forced == 2 || (forced == 0 && nq >= 64 && rows >= 4096);
+    const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.tensor ? rb::kTD : rb::kXD;
+    const uint64_t resident = p.tensor ? 148 : 296;  // CTAs resident on the 148 SMs
+    uint64_t qtiles = std::max<uint64_t>(1, (nq + tq - 1) / tq);
+    uint64_t row_tiles = std::max<uint64_t>(1, (rows + td - 1) / td);
+    uint64_t want = std::max<uint64_t>(1, (4 * resident + qtiles - 1) / qtiles);  // about 4 waves
     uint64_t chunks = std::min(want, row_tiles);
     uint64_t tiles_per_chunk = (row_tiles + chunks - 1) / chunks;
-    p.chunk_rows = tiles_per_chunk * rb::kXD;
+    p.chunk_rows = tiles_per_chunk * td;
     p.chunks = (uint32_t)((row_tiles + tiles_per_chunk - 1) / tiles_per_chunk);
     p.keys_bytes = ((size_t)p.chunks * nq * k * 8 + 255) & ~(size_t)255;
     p.iu_bytes = ((size_t)p.chunks * nq * k * 4 + 255) & ~(size_t)255;
@@ -692,6 +712,8 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     if (!configured) {
         RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(rb::ExactSmem)));
+        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)rb::kTensorSmemBytes));
         configured = true;
     }
     rb::ExactParams ep;
@@ -705,8 +727,13 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     ep.chunk_rows = pl.chunk_rows;
     ep.partial_keys = static_cast<uint64_t*>(workspace);
     ep.partial_iu = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(workspace) + pl.keys_bytes);
-    dim3 grid(pl.chunks, (unsigned)((nq + rb::kXQ - 1) / rb::kXQ));
-    rb::exact_topk_kernel<<<grid, rb::kXThreads, sizeof(rb::ExactSmem), stream>>>(ep);
+    if (pl.tensor) {
+        dim3 grid((unsigned)((nq + rb::kTQ - 1) / rb::kTQ), pl.chunks);  // query tiles fastest: CTAs resident
+        rb::exact_topk_i8_kernel<<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
+    } else {
+        dim3 grid(pl.chunks, (unsigned)((nq + rb::kXQ - 1) / rb::kXQ));
+        rb::exact_topk_kernel<<<grid, rb::kXThreads, sizeof(rb::ExactSmem), stream>>>(ep);
+    }
     rb::MergeParams mp;
     mp.partial_keys = ep.partial_keys;
     mp.parts = pl.chunks;
