@@ -667,21 +667,19 @@ struct ExactPlan {
 
 // RB_EXACT_KERNEL=popc|i8 forces one of the two bit-identical kernels (tests, profiling)
 int exact_kernel_override() {
-    static int mode = [] {
-        char const* e = std::getenv("RB_EXACT_KERNEL");
-        if (!e)
-            return 0;
-        return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : 0;
-    }();
-    return mode;
+    char const* e = std::getenv("RB_EXACT_KERNEL");  // read per call: tests flip it between calls
+    if (!e)
+        return 0;
+    return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : 0;
 }
 
 ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     ExactPlan p;
     const int forced = exact_kernel_override();
-    // the tensor-core tile is 128 queries wide: worth it once at least half a tile is used and there is enough
-    // database to amortise unpacking the queries
-    p.tensor = forced == 2 || (forced == 0 && nq >= 64 && rows >= 4096);
+    // the tensor-core tile is 128 queries wide: worth it once at least half a tile is used and there are enough
+    // pairs per CTA to amortise unpacking the queries and warming up the per-CTA top-k lists (measured crossover
+    // with the POPC kernel: about 1e9 pairs)
+    p.tensor = forced == 2 || (forced == 0 && nq >= 64 && rows * nq >= 2000000000ull);
     const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.tensor ? rb::kTD : rb::kXD;
     const uint64_t resident = p.tensor ? 148 : 296;  // CTAs resident on the 148 SMs
     uint64_t qtiles = std::max<uint64_t>(1, (nq + tq - 1) / tq);
@@ -727,6 +725,14 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     ep.chunk_rows = pl.chunk_rows;
     ep.partial_keys = static_cast<uint64_t*>(workspace);
     ep.partial_iu = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(workspace) + pl.keys_bytes);
+    ep.debug_cycles = nullptr;
+    static unsigned long long* dbg_dev = nullptr;
+    if (pl.tensor && std::getenv("RB_EXACT_DEBUG")) {
+        if (!dbg_dev)
+            RB_CUDA(cudaMalloc(&dbg_dev, 32 * sizeof(unsigned long long)));
+        RB_CUDA(cudaMemsetAsync(dbg_dev, 0, 32 * sizeof(unsigned long long), stream));
+        ep.debug_cycles = dbg_dev;
+    }
     if (pl.tensor) {
         dim3 grid((unsigned)((nq + rb::kTQ - 1) / rb::kTQ), pl.chunks);  // query tiles fastest: CTAs resident
         rb::exact_topk_i8_kernel<<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
@@ -742,6 +748,17 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     mp.keys_out = keys_out;
     rb::merge_topk_kernel<<<(unsigned)((nq + 3) / 4), 128, 4 * (size_t)k * 8, stream>>>(mp);
     RB_CUDA(cudaGetLastError());
+    if (ep.debug_cycles) {
+        unsigned long long h[32];
+        RB_CUDA(cudaStreamSynchronize(stream));
+        RB_CUDA(cudaMemcpy(h, dbg_dev, sizeof(h), cudaMemcpyDeviceToHost));
+        double t = (double)std::max<unsigned long long>(h[31], 1);
+        fprintf(stderr, "[rb exact i8] CTA(0,0) tiles=%llu, cycles per tile\n  producer total %.0f: gload %.0f, wait empty %.0f, "
+                        "wait pd_empty %.0f\n  mma total %.0f: wait tmem_empty %.0f, wait full %.0f\n  epilogue total %.0f: "
+                        "wait pd_full %.0f, wait tmem_full %.0f, tmem ld %.0f, filter %.0f, bar1 %.0f, queue %.0f, bar2+3 %.0f, "
+                        "survivors/tile %.1f\n", h[31], h[0] / t, h[1] / t, h[2] / t, h[3] / t, h[10] / t, h[12] / t, h[13] / t,
+                h[20] / t, h[21] / t, h[22] / t, h[23] / t, h[24] / t, h[25] / t, h[26] / t, h[27] / t, h[28] / t);
+    }
     return {};
 }
 

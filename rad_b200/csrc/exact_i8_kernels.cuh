@@ -27,7 +27,8 @@ constexpr int kTChunkBytes = 128;    // unpacked K bytes per stage (= 128 finger
 constexpr int kTStages = 2;
 constexpr int kTEpiWarps = 4, kTMmaWarp = 4, kTProdWarp0 = 5, kTProdWarps = 8;
 constexpr int kTThreads = (kTEpiWarps + 1 + kTProdWarps) * 32;  // 416
-constexpr int kTQueueCap = kTQ * 32;  // survivors of one 32-column block, worst case
+constexpr int kTQueueCap = kTQ * 8;   // survivors of one 8-column round of a block, worst case (32 queries x 8 per warp)
+constexpr int kTListK = 16;           // top-k lists of up to this k live in shared memory for the whole kernel
 
 // shared-memory operand layout (K-major, SWIZZLE_NONE): 16-byte K pieces of 8 consecutive rows form one contiguous
 // 128-byte core matrix; core matrices step by LBO along K and by SBO along the rows
@@ -42,8 +43,10 @@ struct TensorSmemTail {
     uint32_t pq[kTQ];
     uint32_t pd[2][kTD];
     uint4 thr[kTQ];
-    uint32_t queue[kTQueueCap];
-    uint32_t queue_count;
+    uint32_t queue[kTEpiWarps][kTQueueCap / kTEpiWarps];  // survivors of one warp's 32 queries x 8 columns
+    uint32_t queue_count[kTEpiWarps];
+    unsigned long long lkeys[kTQ][kTListK];  // per-query sorted partial lists (k <= kTListK), written back at the end
+    uint32_t liu[kTQ][kTListK];
     uint32_t tmem_base;
     unsigned long long full[kTStages], empty[kTStages], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
 };
@@ -62,10 +65,10 @@ __device__ __forceinline__ void mbar_wait(void* bar, uint32_t parity) {
     do {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.b32 %0, 1, 0, p;\n\t}"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"  // %3: suspend-time hint, the thread
+            "selp.b32 %0, 1, 0, p;\n\t}"                                        // sleeps instead of re-polling
             : "=r"(done)
-            : "r"(smem_u32(bar)), "r"(parity)
+            : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)
             : "memory");
     } while (!done);
 }
@@ -96,15 +99,22 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 // N >> 3 at [17,23), M >> 4 at [24,29)
 constexpr uint32_t kIdescI8 = (2u << 4) | ((uint32_t)(kTD >> 3) << 17) | ((uint32_t)(kTQ >> 4) << 24);
 
-// 16 fingerprint bits -> 16 bytes of 0/1 (any fixed bit -> K position mapping works: both operands use this one)
-__device__ __forceinline__ uint4 unpack16(uint32_t h) {
-    uint4 o;
-    o.x = ((h & 0xFu) * 0x00204081u) & 0x01010101u;
-    o.y = (((h >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
-    o.z = (((h >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
-    o.w = (((h >> 12) & 0xFu) * 0x00204081u) & 0x01010101u;
-    return o;
+// 32 fingerprint bits -> 32 bytes of 0/1 as two 16-byte K pieces.  Any fixed bit -> K position mapping works as long
+// as both operands use it, so the cheapest one is taken: output word j holds bits j, j+8, j+16, j+24 of the input
+// word, i.e. (w >> j) & 0x01010101 -- one shift and one AND per four bits.
+__device__ __forceinline__ uint4 unpack_half(uint32_t w, int half) {
+    const uint32_t m = 0x01010101u;
+    const int j = half * 4;
+    return make_uint4((w >> j) & m, (w >> (j + 1)) & m, (w >> (j + 2)) & m, (w >> (j + 3)) & m);
 }
+
+#define RB_TICK(slot, expr)                                      \
+    do {                                                         \
+        long long t0_ = dbg ? clock64() : 0;                     \
+        expr;                                                    \
+        if (dbg)                                                 \
+            dbg_acc[slot] += (unsigned long long)(clock64() - t0_); \
+    } while (0)
 
 #define RB_TMEM_LD32(acc, taddr)                                                                                   \
     asm volatile(                                                                                                   \
@@ -121,8 +131,9 @@ __device__ __forceinline__ uint4 unpack16(uint32_t h) {
 
 // grid = (query tiles of 128, database chunks); ExactParams as for exact_topk_kernel with chunk_rows a multiple of kTD
 __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams p) {
-    extern __shared__ unsigned char raw_unaligned[];
-    unsigned char* raw = reinterpret_cast<unsigned char*>(((uintptr_t)raw_unaligned + 1023) & ~(uintptr_t)1023);
+    // no swizzle: the operand descriptors only need 16-byte alignment, which dynamic shared memory guarantees; the
+    // array is used directly so that every access stays in the shared address space (LDS / STS, not generic LD / ST)
+    extern __shared__ __align__(1024) unsigned char raw[];
     unsigned char* smem_a = raw;
     unsigned char* smem_b = raw + kASmemBytes;
     TensorSmemTail& s = *reinterpret_cast<TensorSmemTail*>(raw + kASmemBytes + kTStages * kBStageBytes);
@@ -150,29 +161,32 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
             for (int w = 0; w < 8; ++w)
                 pc += popc4(__ldg(p.queries + (size_t)q * 8 + w));
         s.pq[r] = q < p.query_count ? pc : kXInvalid;
-        s.thr[r] = make_uint4(0, 0, 0, 1);
+        for (int j = 0; j < kTListK; ++j)
+            s.lkeys[r][j] = ~0ull;
+        s.thr[r] = make_uint4(0, 1, 0, 2048);  // list not full: every valid row (|d| < 2048) passes, padding rows do not
     }
     {
-        const uint16_t* q16 = reinterpret_cast<const uint16_t*>(p.queries);
+        const uint32_t* q32 = reinterpret_cast<const uint32_t*>(p.queries);
         for (int idx = tid; idx < kTQ * 64; idx += kTThreads) {
             int r = idx & (kTQ - 1), k16 = idx >> 7;
             uint32_t q = q0 + r;
-            uint32_t h = q < p.query_count ? (uint32_t)__ldg(q16 + (size_t)q * 64 + k16) : 0u;
-            *reinterpret_cast<uint4*>(smem_a + (r >> 3) * kSBO_A + k16 * kLBO + (r & 7) * 16) = unpack16(h);
+            uint32_t w = q < p.query_count ? __ldg(q32 + (size_t)q * 32 + (k16 >> 1)) : 0u;
+            *reinterpret_cast<uint4*>(smem_a + (r >> 3) * kSBO_A + k16 * kLBO + (r & 7) * 16) = unpack_half(w, k16 & 1);
         }
     }
     if (tid == 0) {
         for (int i = 0; i < kTStages; ++i) {
-            mbar_init(&s.full[i], kTProdWarps * 32);
+            mbar_init(&s.full[i], kTProdWarps);  // one arrival per producer WARP (256 arrivals on one word serialise)
             mbar_init(&s.empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s.tmem_full[i], 1);
-            mbar_init(&s.tmem_empty[i], kTEpiWarps * 32);
-            mbar_init(&s.pd_full[i], kTProdWarps * 32);
-            mbar_init(&s.pd_empty[i], kTEpiWarps * 32);
+            mbar_init(&s.tmem_empty[i], kTEpiWarps);
+            mbar_init(&s.pd_full[i], kTProdWarps);
+            mbar_init(&s.pd_empty[i], kTEpiWarps);
         }
-        s.queue_count = 0;
+        for (int i = 0; i < kTEpiWarps; ++i)
+            s.queue_count[i] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kTMmaWarp) {
@@ -185,6 +199,9 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = s.tmem_base;
+    const bool dbg = p.debug_cycles != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+    unsigned long long dbg_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long dbg_start = clock64();
 
     if (warp >= kTProdWarp0) {
         // ================================================================ producers: one database row per thread
@@ -194,30 +211,35 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
             const uint64_t tile = n_tiles - 1 - t;  // highest rows first (see exact_kernels.cuh)
             const uint64_t row = row_begin + tile * kTD + pr;
             uint4 v[8];
+            long long tl0 = dbg ? clock64() : 0;
 #pragma unroll
             for (int c = 0; c < 8; ++c)
                 v[c] = row < row_end ? __ldg(p.db + row * 8 + c) : make_uint4(0, 0, 0, 0);
             uint32_t pc = 0;
+            if (dbg)
+                dbg_acc[0] += (unsigned long long)(clock64() - tl0) + (v[0].x & 0);
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 pc += popc4(v[c]);
                 const uint64_t g = t * 8 + c;
                 const int st = (int)(g & (kTStages - 1));
-                mbar_wait(&s.empty[st], (uint32_t)(((g / kTStages) & 1) ^ 1));
+                RB_TICK(1, mbar_wait(&s.empty[st], (uint32_t)(((g / kTStages) & 1) ^ 1)));
                 unsigned char* dst = my_b + st * kBStageBytes;
                 const uint32_t w[4] = {v[c].x, v[c].y, v[c].z, v[c].w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    uint32_t h = (j & 1) ? (w[j >> 1] >> 16) : (w[j >> 1] & 0xFFFFu);
-                    *reinterpret_cast<uint4*>(dst + j * kLBO) = unpack16(h);
-                }
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4*>(dst + j * kLBO) = unpack_half(w[j >> 1], j & 1);
                 fence_proxy_async();
-                mbar_arrive(&s.full[st]);
+                __syncwarp();
+                if (lane == 0)
+                    mbar_arrive(&s.full[st]);
             }
             const int a = (int)(t & 1);
-            mbar_wait(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));  // the epilogue of tile t-2 is done with pd[a]
+            RB_TICK(2, mbar_wait(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));  // epilogue of tile t-2 done with pd[a]
             s.pd[a][pr] = row < row_end ? pc : kXInvalid;
-            mbar_arrive(&s.pd_full[a]);
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&s.pd_full[a]);
         }
     } else if (warp == kTMmaWarp) {
         // ================================================================ MMA issuer
@@ -225,12 +247,12 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
         const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), kLBO, kSBO_B);
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const int a = (int)(t & 1);
-            mbar_wait(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
+            RB_TICK(1, mbar_wait(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
             tc_fence_after();
             for (int c = 0; c < 8; ++c) {
                 const uint64_t g = t * 8 + c;
                 const int st = (int)(g & (kTStages - 1));
-                mbar_wait(&s.full[st], (uint32_t)((g / kTStages) & 1));
+                RB_TICK(2, mbar_wait(&s.full[st], (uint32_t)((g / kTStages) & 1)));
                 tc_fence_after();
                 if (lane == 0) {
 #pragma unroll
@@ -251,66 +273,132 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
         // ================================================================ epilogue: thread = one query of the tile
         const int ql = warp * 32 + lane;
         const uint32_t pqv = s.pq[ql];
+        const bool smem_lists = p.k <= (uint32_t)kTListK;
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;
             const int a = (int)(t & 1);
-            mbar_wait(&s.pd_full[a], (uint32_t)((t >> 1) & 1));
-            mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1));
+            RB_TICK(0, mbar_wait(&s.pd_full[a], (uint32_t)((t >> 1) & 1)));
+            RB_TICK(1, mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1)));
             tc_fence_after();
             // 32-column blocks from the HIGHEST rows down: the thresholds move between blocks, and a row that only ties
             // the k-th distance must never displace a higher slot (same invariant as the tile order)
             for (int b = kTD / 32 - 1; b >= 0; --b) {
                 uint32_t acc[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * kTD + b * 32);
+                long long te0 = dbg ? clock64() : 0;
                 RB_TMEM_LD32(acc, taddr);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                long long te1 = dbg ? clock64() : 0;
                 if (b == 0) {  // the accumulator stage is free as soon as the last block is in registers
                     tc_fence_before();
-                    mbar_arrive(&s.tmem_empty[a]);
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(&s.tmem_empty[a]);
                 }
-                const uint4 th = s.thr[ql];
-                if (pqv != kXInvalid) {
+                // exact integer filter, 3 instructions per pair: the pair passes iff
+                //     i * A + w > B + y * |d|      (A = u_t + i_t, y = i_t, B = i_t |q|, w = 0; see exact_kernels.cuh)
+                // i.e. iff  dlt = (y |d| + B - w) - i A  is negative; its sign bit is funnel-shifted into one of four
+                // independent 8-bit masks (pair 8 r + j of the block ends up at bit 7 - j of mask r).  Padding rows
+                // (|d| = 0xFFFF, i = 0) never pass.
+                uint32_t hm[4] = {0, 0, 0, 0};
+                {
+                    const uint4 th = s.thr[ql];
+                    const uint32_t neg_a = 0u - th.x, bw = th.z - th.w, y = th.y;
+                    const uint4* pd4 = reinterpret_cast<const uint4*>(&s.pd[a][b * 32]);
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const uint32_t pdv = s.pd[a][b * 32 + j];
-                        const uint32_t i = acc[j];
-                        if (pdv != kXInvalid && i * th.x + th.w > th.z + th.y * pdv) {
-                            uint32_t at = atomicAdd(&s.queue_count, 1u);
-                            s.queue[at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + j) << 16) | i;
+                    for (int g = 0; g < 8; ++g) {
+                        const uint4 pv = pd4[g];
+                        const uint32_t pdv[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            uint32_t r1, dlt;  // two multiply-adds, kept from being re-associated into three
+                            asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r1) : "r"(y), "r"(pdv[e]), "r"(bw));
+                            asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(dlt) : "r"(acc[g * 4 + e]), "r"(neg_a), "r"(r1));
+                            hm[g >> 1] = __funnelshift_l(dlt, hm[g >> 1], 1);
                         }
                     }
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                const uint32_t qn = s.queue_count;
-                for (uint32_t base = 0; base < qn; base += 32) {
-                    uint32_t e = base + lane < qn ? s.queue[base + lane] : 0xFFFFFFFFu;
-                    uint32_t mine = __ballot_sync(RB_FULL_MASK, base + lane < qn && (int)((e >> 24) & 3) == warp);
-                    while (mine) {
-                        int jj = __ffs((int)mine) - 1;
-                        mine &= mine - 1;
-                        uint32_t ev = __shfl_sync(RB_FULL_MASK, e, jj);
-                        uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
-                        uint32_t u = s.pq[eq] + s.pd[a][dl] - i;
-                        uint32_t slot = (uint32_t)(p.slot_base + row_begin + tile * kTD + dl);
-                        uint64_t key = ((uint64_t)exact_distance_bits(i, u) << 32) | (uint32_t)~slot;
-                        size_t off = ((size_t)chunk * p.query_count + q0 + eq) * p.k;
-                        glist_insert(p.partial_keys + off, p.partial_iu + off, p.k, key, i | ((u ? u : 1u) << 16));
-                        if (p.partial_keys[off + p.k - 1] != ~0ull) {
-                            uint32_t iu = p.partial_iu[off + p.k - 1];
-                            uint32_t it_ = iu & 0xFFFFu, ut = iu >> 16;
-                            if (lane == 0)
-                                s.thr[eq] = make_uint4(ut + it_, it_, it_ * s.pq[eq], 0);
+                const uint32_t any_hit = pqv == kXInvalid ? 0u : (hm[0] | hm[1] | hm[2] | hm[3]);
+                long long te2 = dbg ? clock64() : 0, te3 = te2;
+                uint32_t qn_total = 0;
+                if (__any_sync(RB_FULL_MASK, any_hit != 0)) {
+                    // rare: rounds of 8 columns from the HIGHEST rows down (round r = columns 8 r .. 8 r + 7); a survivor
+                    // always belongs to one of this warp's own 32 queries, so the slow path is warp-local
+#pragma unroll
+                    for (int r = 3; r >= 0; --r) {
+                        uint32_t hit = pqv == kXInvalid ? 0u : hm[r];
+                        if (!__any_sync(RB_FULL_MASK, hit != 0))
+                            continue;
+                        while (hit) {
+                            const int j = 7 - (31 - __clz((int)hit));  // bit 7 - j <-> column 8 r + j
+                            hit &= ~(0x80u >> j);
+                            uint32_t iv = 0;
+#pragma unroll
+                            for (int e = 0; e < 8; ++e)  // acc[] lives in registers: select without dynamic indexing
+                                iv = (e == j) ? acc[r * 8 + e] : iv;
+                            uint32_t at = atomicAdd(&s.queue_count[warp], 1u);
+                            s.queue[warp][at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + r * 8 + j) << 16) | iv;
                         }
+                        __syncwarp();
+                        const uint32_t qn = s.queue_count[warp];
+                        qn_total += qn;
+                        for (uint32_t base = 0; base < qn; base += 32) {
+                            uint32_t e = base + lane < qn ? s.queue[warp][base + lane] : 0xFFFFFFFFu;
+                            for (uint32_t jj = 0; jj < 32 && base + jj < qn; ++jj) {
+                                uint32_t ev = __shfl_sync(RB_FULL_MASK, e, (int)jj);
+                                uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
+                                uint32_t u = s.pq[eq] + s.pd[a][dl] - i;
+                                uint32_t slot = (uint32_t)(p.slot_base + row_begin + tile * kTD + dl);
+                                uint64_t key = ((uint64_t)exact_distance_bits(i, u) << 32) | (uint32_t)~slot;
+                                uint64_t* lk;
+                                uint32_t* li;
+                                if (smem_lists) {
+                                    lk = reinterpret_cast<uint64_t*>(&s.lkeys[eq][0]);
+                                    li = &s.liu[eq][0];
+                                } else {
+                                    size_t off = ((size_t)chunk * p.query_count + q0 + eq) * p.k;
+                                    lk = p.partial_keys + off;
+                                    li = p.partial_iu + off;
+                                }
+                                glist_insert(lk, li, p.k, key, i | ((u ? u : 1u) << 16));
+                                if (lk[p.k - 1] != ~0ull) {
+                                    uint32_t iu = li[p.k - 1];
+                                    uint32_t it_ = iu & 0xFFFFu, ut = iu >> 16;
+                                    if (lane == 0)
+                                        s.thr[eq] = make_uint4(ut + it_, it_, it_ * s.pq[eq], 0);
+                                }
+                                __syncwarp();
+                            }
+                        }
+                        if (lane == 0)
+                            s.queue_count[warp] = 0;
                         __syncwarp();
                     }
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                if (tid == 0)
-                    s.queue_count = 0;
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (dbg) {
+                    long long te5 = clock64();
+                    dbg_acc[2] += (unsigned long long)(te1 - te0);
+                    dbg_acc[3] += (unsigned long long)(te2 - te1);
+                    dbg_acc[4] += (unsigned long long)(te3 - te2);
+                    dbg_acc[5] += (unsigned long long)(te5 - te3);
+                    dbg_acc[7] += qn_total;
+                }
             }
-            mbar_arrive(&s.pd_empty[a]);
+            if (lane == 0)
+                mbar_arrive(&s.pd_empty[a]);
         }
+        if (smem_lists && pqv != kXInvalid) {  // publish this query's partial list
+            size_t off = ((size_t)chunk * p.query_count + q0 + ql) * p.k;
+            for (uint32_t j = 0; j < p.k; ++j)
+                p.partial_keys[off + j] = s.lkeys[ql][j];
+        }
+    }
+    if (dbg && (warp == kTProdWarp0 || warp == kTMmaWarp || warp == 0)) {
+        int role = warp == kTProdWarp0 ? 0 : warp == kTMmaWarp ? 1 : 2;
+        p.debug_cycles[role * 10 + 0] = (unsigned long long)(clock64() - dbg_start);
+        for (int i = 0; i < 8; ++i)
+            p.debug_cycles[role * 10 + 1 + i] = dbg_acc[i];
+        p.debug_cycles[31] = n_tiles;
     }
     __syncthreads();
     if (warp == kTMmaWarp)

@@ -14,6 +14,14 @@ from rad_b200.index import Index
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["popc", "i8"])
+def exact_kernel(request, monkeypatch):
+    """Every test of this module runs against BOTH exact-search kernels: the POPC-pipe kernel and the tcgen05 int8
+    tensor-core kernel (rad_b200/csrc/exact_i8_kernels.cuh); the library reads RB_EXACT_KERNEL on every call."""
+    monkeypatch.setenv("RB_EXACT_KERNEL", request.param)
+    return request.param
+
+
 def _bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
 
