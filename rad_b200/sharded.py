@@ -76,6 +76,10 @@ class ShardedExactSearch:
         self._ws = None
 
     def search(self, d_queries, k: int = 10):
+        return self.merge(self.search_local(d_queries, k), k)
+
+    def search_local(self, d_queries, k: int = 10):
+        """This rank's shard only: ``int64 [Q, k]`` keys carrying GLOBAL slots, before the exchange."""
         torch = self._torch
         nq = int(d_queries.shape[0])
         need = int(self._lib.rb_exact_topk_workspace_bytes(self.rows, nq, k))
@@ -87,7 +91,7 @@ class ShardedExactSearch:
         self._lib.rb_exact_topk_device(self.d_shard.data_ptr(), self.rows, self.slot_base, d_queries.data_ptr(), nq,
                                        k, part.data_ptr(), self._ws.data_ptr(), need, stream, C.byref(err))
         self._native.check(err)
-        return self.merge(part, k)
+        return part
 
     def merge(self, part, k: int):
         """All-gather the per-rank ``[Q, k]`` keys and merge them on the device (no-op for a single rank)."""
