@@ -36,6 +36,7 @@ struct WarpScratch {
     uint32_t* bloom;   // 2^bloom_log2 bits
     uint4* kept;       // kMaxWidth fingerprints (32 x 8 uint4) for the selection heuristic
     uint64_t* sel;     // kMaxWidth selected keys
+    uint64_t* pend;    // 32 qualified candidates not yet merged into the list
     uint32_t* ids;     // 32 staging ids
     uint32_t bloom_log2;
 };
@@ -43,7 +44,7 @@ struct WarpScratch {
 // kept_rows = fingerprints the selection heuristic may keep (= connectivity in the insert / search kernels)
 __host__ __device__ inline size_t warp_scratch_bytes(uint32_t ef, uint32_t bloom_log2, uint32_t kept_rows) {
     size_t list = ((size_t)ef * 8 + 15) & ~(size_t)15;
-    return list + ((size_t)1 << bloom_log2) / 8 + (size_t)kept_rows * 128 + kMaxWidth * 8 + 32 * 4;
+    return list + ((size_t)1 << bloom_log2) / 8 + (size_t)kept_rows * 128 + kMaxWidth * 8 + 32 * 8 + 32 * 4;
 }
 
 __device__ __forceinline__ WarpScratch carve_scratch(unsigned char* base, uint32_t ef, uint32_t bloom_log2,
@@ -56,6 +57,8 @@ __device__ __forceinline__ WarpScratch carve_scratch(unsigned char* base, uint32
     base += list;
     w.sel = reinterpret_cast<uint64_t*>(base);
     base += kMaxWidth * 8;
+    w.pend = reinterpret_cast<uint64_t*>(base);
+    base += 32 * 8;
     w.bloom = reinterpret_cast<uint32_t*>(base);
     base += ((size_t)1 << bloom_log2) / 8;
     w.ids = reinterpret_cast<uint32_t*>(base);
@@ -304,11 +307,17 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
     len = 1;
     __syncwarp();
     uint32_t hint = 0;  // every entry before `hint` is expanded
+    // Candidates that passed the filter wait in w.pend (lane j's copy in `pk`) and are merged 32 at a time.  The
+    // traversal is exactly the one of a list kept merged after every expansion: the entries expanded next are the
+    // smallest unexpanded keys of list + pending, and pending is merged first whenever membership of the `ef` best
+    // could depend on it (see the flush rule below).
+    uint32_t pn = 0;
+    uint64_t pk = ~0ull;
     // rows of at most 16 links are expanded TWO list entries at a time: lanes 0-15 read one row, lanes 16-31 the other
     const uint32_t row_width = level == 0 ? g.m0 : g.m;
     const bool two = row_width <= 16;
     for (;;) {
-        // first (two) unexpanded entries
+        // first (two) unexpanded entries of the list
         uint32_t pos1 = 0xFFFFFFFFu, pos2 = 0xFFFFFFFFu;
         for (uint32_t base = hint; base < len; base += 32) {
             uint32_t idx = base + lane;
@@ -325,18 +334,62 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
                     break;
             }
         }
+        if (pn) {
+            // An entry at list position p has at most p + pn smaller keys, a pending key below it fewer: while the
+            // last scanned position + pn < ef, everything at or below that entry is among the ef best.  Otherwise
+            // (or when the list ran out of open entries) merge now and look again.
+            const uint32_t last = two ? pos2 : pos1;
+            if (last == 0xFFFFFFFFu || last + pn >= ef) {
+                uint32_t at = list_merge(w.list, len, ef, pk, (uint32_t)lane < pn);
+                if (at < hint)
+                    hint = at;
+                pn = 0;
+                pk = ~0ull;
+                continue;
+            }
+        }
         if (pos1 == 0xFFFFFFFFu)
             break;
-        const bool both = pos2 != 0xFFFFFFFFu;
+        bool both = pos2 != 0xFFFFFFFFu;
         uint64_t key1 = w.list[pos1];
-        uint64_t key2 = both ? w.list[pos2] : 0ull;
-        __syncwarp();
-        if (lane == 0) {
-            w.list[pos1] = key1 | 1ull;
-            if (both)
-                w.list[pos2] = key2 | 1ull;
+        uint64_t key2 = both ? w.list[pos2] : ~0ull;
+        uint32_t src1 = 32, src2 = 33;  // 32/33 = list entry pos1/pos2, < 32 = pending lane
+        if (pn) {
+            // pending keys below the last scanned entry compete for the two places (pn > 0 implies a full scan)
+            uint32_t cand = __ballot_sync(RB_FULL_MASK, !(pk & 1ull) && pk < (two ? key2 : key1));
+            while (cand) {
+                int l = __ffs((int)cand) - 1;
+                cand &= cand - 1;
+                uint64_t x = __shfl_sync(RB_FULL_MASK, pk, l);
+                if (x < key1) {
+                    key2 = key1;
+                    src2 = src1;
+                    key1 = x;
+                    src1 = (uint32_t)l;
+                } else if (x < key2) {
+                    key2 = x;
+                    src2 = (uint32_t)l;
+                }
+            }
         }
-        hint = (both ? pos2 : pos1) + 1;
+        __syncwarp();
+        // mark the chosen entries expanded, wherever they live
+        if ((uint32_t)lane == src1 || ((uint32_t)lane == src2 && both)) {
+            pk |= 1ull;
+            w.pend[lane] = pk;
+        }
+        if (lane == 0) {
+            if (src1 == 32)
+                w.list[pos1] = key1 | 1ull;
+            if (both && src2 == 33)
+                w.list[pos2] = key2 | 1ull;
+            else if (both && src2 == 32)
+                w.list[pos1] = key2 | 1ull;
+        }
+        {
+            const bool took1 = src1 == 32 || (both && src2 == 32), took2 = both && src2 == 33;
+            hint = took2 ? pos2 + 1 : took1 ? pos1 + 1 : pos1;
+        }
         tc.expansions += both ? 2 : 1;
         uint32_t nid = RB_EMPTY;
         {
@@ -368,9 +421,24 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         __syncwarp();
         uint32_t bits = warp_eval(g.fp, q4, id, cnt);
         tc.distances += cnt;
-        uint32_t at = list_merge(w.list, len, ef, make_key(bits, id), (uint32_t)lane < cnt);
-        if (at < hint)
-            hint = at;
+        // qualify against the (possibly stale, hence only looser) worst list entry and park in pending
+        const uint64_t key = make_key(bits, id);
+        bool keep = (uint32_t)lane < cnt && (len < ef || key < (w.list[ef - 1] & ~1ull));
+        const uint32_t kmask = __ballot_sync(RB_FULL_MASK, keep);
+        const uint32_t kc = __popc(kmask);
+        if (!kc)
+            continue;
+        if (pn + kc > 32) {
+            uint32_t at = list_merge(w.list, len, ef, pk, (uint32_t)lane < pn);
+            if (at < hint)
+                hint = at;
+            pn = 0;
+        }
+        if (keep)
+            w.pend[pn + __popc(kmask & ((1u << lane) - 1u))] = key;
+        pn += kc;
+        __syncwarp();
+        pk = (uint32_t)lane < pn ? w.pend[lane] : ~0ull;
     }
     return len;
 }
