@@ -95,6 +95,63 @@ __device__ __forceinline__ uint32_t warp_eval(const uint4* __restrict__ fp, uint
     return cnt <= 16 ? warp_eval_n<4>(fp, q4, ids, cnt) : warp_eval_n<8>(fp, q4, ids, cnt);
 }
 
+// The beam-search form: a fingerprint is fetched by a group of FOUR lanes (two LDG.128 per lane, slices sub and sub + 4),
+// so one round covers 8 candidates and the per-round overhead (id broadcast, address, reduction) is paid half as often.
+// The per-round partial sums are reduced with a transposing butterfly: after it lane (grp, sub) holds the complete
+// counts of candidate `cand` = sub * 8 + grp (sub < ROUNDS), 3 shuffles for 4 rounds instead of 4 x 3.
+// qa / qb = query slices (lane & 3) and (lane & 3) + 4.  Returns the order key bits of candidate `cand` (0xFFFFFFFF: none).
+template <int ROUNDS>
+__device__ __forceinline__ uint32_t warp_eval4_n(const uint4* __restrict__ fp, uint4 qa, uint4 qb, uint32_t ids,
+                                                 uint32_t cnt, uint32_t& cand) {
+    static_assert(ROUNDS == 1 || ROUNDS == 2 || ROUNDS == 4, "rounds");
+    const int lane = threadIdx.x & 31, sub = lane & 3, grp = lane >> 2;
+    uint4 a[ROUNDS], b[ROUNDS];
+#pragma unroll
+    for (int r = 0; r < ROUNDS; ++r) {
+        uint32_t j = r * 8 + grp;
+        uint32_t id = __shfl_sync(RB_FULL_MASK, ids, j & 31);
+        const bool on = j < cnt;
+        a[r] = on ? load_slice(fp, id, sub) : make_uint4(0, 0, 0, 0);
+        b[r] = on ? load_slice(fp, id, sub + 4) : make_uint4(0, 0, 0, 0);
+    }
+    uint32_t v[ROUNDS];
+#pragma unroll
+    for (int r = 0; r < ROUNDS; ++r) {
+        v[r] = 0;
+        if (r == 0 || (uint32_t)(r * 8) < cnt)  // warp-uniform: a round without candidates costs nothing
+            v[r] = (popc4_and(a[r], qa) + popc4_and(b[r], qb)) | ((popc4_or(a[r], qa) + popc4_or(b[r], qb)) << 16);
+    }
+    uint32_t k;
+    if (ROUNDS == 4) {
+        const bool b0 = sub & 1, b1 = sub & 2;
+        uint32_t k0 = (b0 ? v[1] : v[0]) + __shfl_xor_sync(RB_FULL_MASK, b0 ? v[0] : v[1], 1);
+        uint32_t k1 = (b0 ? v[3] : v[2]) + __shfl_xor_sync(RB_FULL_MASK, b0 ? v[2] : v[3], 1);
+        k = (b1 ? k1 : k0) + __shfl_xor_sync(RB_FULL_MASK, b1 ? k0 : k1, 2);
+        cand = (uint32_t)(sub * 8 + grp);
+    } else if (ROUNDS == 2) {
+        const bool b0 = sub & 1;
+        k = (b0 ? v[1] : v[0]) + __shfl_xor_sync(RB_FULL_MASK, b0 ? v[0] : v[1], 1);
+        k += __shfl_xor_sync(RB_FULL_MASK, k, 2);
+        cand = sub < 2 ? (uint32_t)(sub * 8 + grp) : 0xFFFFFFFFu;
+    } else {
+        k = v[0] + __shfl_xor_sync(RB_FULL_MASK, v[0], 1);
+        k += __shfl_xor_sync(RB_FULL_MASK, k, 2);
+        cand = sub == 0 ? (uint32_t)grp : 0xFFFFFFFFu;
+    }
+    if (cand >= cnt)
+        cand = 0xFFFFFFFFu;
+    return order_key_bits(k & 0xFFFFu, k >> 16);
+}
+
+__device__ __forceinline__ uint32_t warp_eval4(const uint4* __restrict__ fp, uint4 qa, uint4 qb, uint32_t ids,
+                                               uint32_t cnt, uint32_t& cand) {
+    if (cnt <= 8)
+        return warp_eval4_n<1>(fp, qa, qb, ids, cnt, cand);
+    if (cnt <= 16)
+        return warp_eval4_n<2>(fp, qa, qb, ids, cnt, cand);
+    return warp_eval4_n<4>(fp, qa, qb, ids, cnt, cand);
+}
+
 // distance of the query to ONE slot, result in every lane
 __device__ __forceinline__ uint32_t warp_eval_one(const uint4* __restrict__ fp, uint4 q4, uint32_t slot) {
     uint4 a = load_slice(fp, slot, threadIdx.x & 7);
@@ -313,6 +370,12 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
     // could depend on it (see the flush rule below).
     uint32_t pn = 0;
     uint64_t pk = ~0ull;
+    // query slices for the 4-lane evaluation (q4 = slice lane & 7 is held by lanes 0-7)
+    uint4 qa, qb;
+    qa.x = __shfl_sync(RB_FULL_MASK, q4.x, lane & 3), qa.y = __shfl_sync(RB_FULL_MASK, q4.y, lane & 3);
+    qa.z = __shfl_sync(RB_FULL_MASK, q4.z, lane & 3), qa.w = __shfl_sync(RB_FULL_MASK, q4.w, lane & 3);
+    qb.x = __shfl_sync(RB_FULL_MASK, q4.x, (lane & 3) + 4), qb.y = __shfl_sync(RB_FULL_MASK, q4.y, (lane & 3) + 4);
+    qb.z = __shfl_sync(RB_FULL_MASK, q4.z, (lane & 3) + 4), qb.w = __shfl_sync(RB_FULL_MASK, q4.w, (lane & 3) + 4);
     // rows of at most 16 links are expanded TWO list entries at a time: lanes 0-15 read one row, lanes 16-31 the other
     const uint32_t row_width = level == 0 ? g.m0 : g.m;
     const bool two = row_width <= 16;
@@ -419,11 +482,12 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         __syncwarp();
         uint32_t id = (uint32_t)lane < cnt ? w.ids[lane] : 0u;
         __syncwarp();
-        uint32_t bits = warp_eval(g.fp, q4, id, cnt);
+        uint32_t cand;  // the candidate whose distance this lane received
+        uint32_t bits = warp_eval4(g.fp, qa, qb, id, cnt, cand);
         tc.distances += cnt;
         // qualify against the (possibly stale, hence only looser) worst list entry and park in pending
-        const uint64_t key = make_key(bits, id);
-        bool keep = (uint32_t)lane < cnt && (len < ef || key < (w.list[ef - 1] & ~1ull));
+        const uint64_t key = make_key(bits, __shfl_sync(RB_FULL_MASK, id, cand & 31));
+        bool keep = cand != 0xFFFFFFFFu && (len < ef || key < (w.list[ef - 1] & ~1ull));
         const uint32_t kmask = __ballot_sync(RB_FULL_MASK, keep);
         const uint32_t kc = __popc(kmask);
         if (!kc)
