@@ -331,12 +331,20 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
 int traversal_variant(size_t smem) {
     const size_t per_sm = 227 * 1024;
     size_t fit = per_sm / (smem + 1024);  // 1 KB of system-reserved shared memory per CTA
-    return fit >= 8 ? 8 : fit >= 6 ? 6 : 4;
+    return fit >= 8 ? 8 : fit >= 4 ? (int)fit : 4;
 }
 
-template <typename K4, typename K6, typename K8>
-std::string configure_variant(int variant, K4 k4, K6 k6, K8 k8, size_t smem, int& blocks_per_sm) {
-    const void* fn = variant == 8 ? (const void*)k8 : variant == 6 ? (const void*)k6 : (const void*)k4;
+// expands to KERNEL<4..8> according to the run-time variant
+#define RB_FOR_VARIANT(variant, STMT)                       \
+    switch (variant) {                                      \
+        case 8: { constexpr int V = 8; STMT; } break;       \
+        case 7: { constexpr int V = 7; STMT; } break;       \
+        case 6: { constexpr int V = 6; STMT; } break;       \
+        case 5: { constexpr int V = 5; STMT; } break;       \
+        default: { constexpr int V = 4; STMT; } break;      \
+    }
+
+std::string configure_variant(const void* fn, size_t smem, int& blocks_per_sm) {
     RB_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     RB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, fn, rb::kWarpsPerBlock * 32, smem));
     return {};
@@ -348,8 +356,9 @@ std::string configure_traversal_kernels(rb_index* ix) {
     if (d.insert_cfg_ef != ix->host.ef_add) {
         size_t smem = rb::warp_scratch_bytes(ix->host.ef_add, bloom, m) * rb::kWarpsPerBlock;
         d.insert_variant = traversal_variant(smem);
-        std::string err = configure_variant(d.insert_variant, rb::insert_kernel<4>, rb::insert_kernel<6>,
-                                            rb::insert_kernel<8>, smem, d.insert_blocks_per_sm);
+        const void* fn = nullptr;
+        RB_FOR_VARIANT(d.insert_variant, fn = (const void*)rb::insert_kernel<V>);
+        std::string err = configure_variant(fn, smem, d.insert_blocks_per_sm);
         if (!err.empty())
             return err;
         if (d.insert_blocks_per_sm < 1)
@@ -364,8 +373,9 @@ std::string configure_search_kernel(rb_index* ix, uint32_t ef) {
     if (d.search_cfg_ef != ef) {
         size_t smem = rb::warp_scratch_bytes(ef, ix->opts.bloom_bits_log2, ix->host.m) * rb::kWarpsPerBlock;
         d.search_variant = traversal_variant(smem);
-        std::string err = configure_variant(d.search_variant, rb::search_kernel<4>, rb::search_kernel<6>,
-                                            rb::search_kernel<8>, smem, d.search_blocks_per_sm);
+        const void* fn = nullptr;
+        RB_FOR_VARIANT(d.search_variant, fn = (const void*)rb::search_kernel<V>);
+        std::string err = configure_variant(fn, smem, d.search_blocks_per_sm);
         if (!err.empty())
             return err;
         if (d.search_blocks_per_sm < 1)
@@ -487,12 +497,8 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
                                                          (size_t)d.sm_count * d.insert_blocks_per_sm);
             if (time_kernels)
                 RB_CUDA(tick());
-            if (d.insert_variant == 8)
-                rb::insert_kernel<8><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
-            else if (d.insert_variant == 6)
-                rb::insert_kernel<6><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
-            else
-                rb::insert_kernel<4><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip);
+            RB_FOR_VARIANT(d.insert_variant,
+                           (rb::insert_kernel<V><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip)));
             if (time_kernels)
                 RB_CUDA(tick());
             const size_t pairs = (size_t)b.tasks * h.m;
@@ -837,12 +843,8 @@ std::string search_on_device(rb_index* ix, uint4 const* d_queries, size_t nq, si
         size_t smem = rb::warp_scratch_bytes(ef, ix->opts.bloom_bits_log2, h.m) * rb::kWarpsPerBlock;
         unsigned blocks = (unsigned)std::min<size_t>((nq + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
                                                      (size_t)d.sm_count * d.search_blocks_per_sm);
-        if (d.search_variant == 8)
-            rb::search_kernel<8><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
-        else if (d.search_variant == 6)
-            rb::search_kernel<6><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
-        else
-            rb::search_kernel<4><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp);
+        RB_FOR_VARIANT(d.search_variant,
+                       (rb::search_kernel<V><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(sp)));
         launches = 1;
     }
     RB_CUDA(cudaGetLastError());

@@ -34,8 +34,8 @@ __device__ __forceinline__ uint32_t key_bits(uint64_t key) { return (uint32_t)(k
 struct WarpScratch {
     uint64_t* list;    // ef entries
     uint32_t* bloom;   // 2^bloom_log2 bits
-    uint4* kept;       // kMaxWidth fingerprints (32 x 8 uint4) for the selection heuristic
-    uint64_t* sel;     // kMaxWidth selected keys
+    uint4* kept;       // kept_rows fingerprints for the selection heuristic   } alias the Bloom filter: the filter is
+    uint64_t* sel;     // kMaxWidth selected keys                              } dead once a beam search has ended
     uint64_t* pend;    // 32 qualified candidates not yet merged into the list
     uint32_t* ids;     // 32 staging ids
     uint32_t bloom_log2;
@@ -44,23 +44,23 @@ struct WarpScratch {
 // kept_rows = fingerprints the selection heuristic may keep (= connectivity in the insert / search kernels)
 __host__ __device__ inline size_t warp_scratch_bytes(uint32_t ef, uint32_t bloom_log2, uint32_t kept_rows) {
     size_t list = ((size_t)ef * 8 + 15) & ~(size_t)15;
-    return list + ((size_t)1 << bloom_log2) / 8 + (size_t)kept_rows * 128 + kMaxWidth * 8 + 32 * 8 + 32 * 4;
+    size_t bloom = ((size_t)1 << bloom_log2) / 8, select = (size_t)kept_rows * 128 + kMaxWidth * 8;
+    return list + (bloom > select ? bloom : select) + 32 * 8 + 32 * 4;
 }
 
 __device__ __forceinline__ WarpScratch carve_scratch(unsigned char* base, uint32_t ef, uint32_t bloom_log2,
                                                      uint32_t kept_rows) {
     WarpScratch w;
     size_t list = ((size_t)ef * 8 + 15) & ~(size_t)15;
-    w.kept = reinterpret_cast<uint4*>(base);
-    base += (size_t)kept_rows * 128;
+    size_t bloom = ((size_t)1 << bloom_log2) / 8, select = (size_t)kept_rows * 128 + kMaxWidth * 8;
     w.list = reinterpret_cast<uint64_t*>(base);
     base += list;
-    w.sel = reinterpret_cast<uint64_t*>(base);
-    base += kMaxWidth * 8;
     w.pend = reinterpret_cast<uint64_t*>(base);
     base += 32 * 8;
     w.bloom = reinterpret_cast<uint32_t*>(base);
-    base += ((size_t)1 << bloom_log2) / 8;
+    w.kept = reinterpret_cast<uint4*>(base);
+    w.sel = reinterpret_cast<uint64_t*>(base + (size_t)kept_rows * 128);
+    base += bloom > select ? bloom : select;
     w.ids = reinterpret_cast<uint32_t*>(base);
     w.bloom_log2 = bloom_log2;
     return w;
