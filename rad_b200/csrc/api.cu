@@ -540,7 +540,46 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         }
     }
     RB_CUDA(cudaEventRecord(d.ev_end, d.stream));
-    RB_CUDA(cudaStreamSynchronize(d.stream));
+    // Host bookkeeping of the new rows.  Without a progress callback nothing can cut the schedule short, so it runs
+    // HERE, while the device is still working through the batches, and is undone if the device reports an error.
+    const int32_t old_max_level = h.max_level;
+    const uint64_t old_entry = h.entry;
+    auto commit = [&](size_t count) {
+        int32_t top = h.max_level;
+        uint64_t top_slot = h.entry;
+        for (size_t i = 0; i < count; ++i) {
+            size_t slot = old_size + i;
+            if (slot == 0 || new_levels[i] > top) {
+                top = new_levels[i];
+                top_slot = slot;
+            }
+        }
+        h.keys.insert(h.keys.end(), keys, keys + count);
+        h.levels.insert(h.levels.end(), new_levels.begin(), new_levels.begin() + count);
+        h.upper_off.resize(old_size + count + 1);
+        for (size_t i = 0; i < count; ++i)
+            h.upper_off[old_size + i + 1] = h.upper_off[old_size + i] + (uint64_t)new_levels[i];
+        h.max_level = top;
+        h.entry = top_slot;
+        h.note_new_keys(keys, count);
+    };
+    const bool early = !progress && !cancelled && inserted == n;
+    if (early)
+        commit(n);
+    {
+        cudaError_t e = cudaStreamSynchronize(d.stream);
+        if (e == cudaSuccess)
+            e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            if (early)
+                h.truncate_rows(old_size, old_max_level, old_entry);
+            for (cudaEvent_t ev : marks)
+                cudaEventDestroy(ev);
+            for (cudaEvent_t ev : ticks)
+                cudaEventDestroy(ev);
+            return std::string("CUDA error: ") + cudaGetErrorString(e);
+        }
+    }
     for (cudaEvent_t ev : marks)
         cudaEventDestroy(ev);
     RB_CUDA(cudaGetLastError());
@@ -570,23 +609,8 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
 
     // commit what was inserted (everything unless a debug cap or a cancellation cut the schedule short)
     accepted = inserted;
-    max_level = h.max_level;
-    entry = h.entry;
-    for (size_t i = 0; i < accepted; ++i) {
-        size_t slot = old_size + i;
-        if (slot == 0 || new_levels[i] > max_level) {
-            max_level = new_levels[i];
-            entry = slot;
-        }
-    }
-    h.keys.insert(h.keys.end(), keys, keys + accepted);
-    h.levels.insert(h.levels.end(), new_levels.begin(), new_levels.begin() + accepted);
-    h.upper_off.resize(old_size + accepted + 1);
-    for (size_t i = 0; i < accepted; ++i)
-        h.upper_off[old_size + i + 1] = h.upper_off[old_size + i] + (uint64_t)new_levels[i];
-    h.max_level = max_level;
-    h.entry = entry;
-    h.note_new_keys(keys, accepted);
+    if (!early)
+        commit(accepted);
     d.rows = old_size + accepted;
     d.upper_rows = h.upper_off[old_size + accepted];
     ix->device_graph_valid = true;

@@ -84,18 +84,40 @@ int64_t KeyMap::find(uint64_t key) const {
 // ------------------------------------------------------------------------------------------------ level stream
 // minstd_rand0 + libstdc++ generate_canonical<double, 53> (two draws, low digit first), index.hpp:3867-3871
 static inline uint32_t minstd_next(uint32_t& state) {
-    state = (uint32_t)((uint64_t)state * 16807ull % 2147483647ull);
+    // x * 16807 mod (2^31 - 1) without a division: fold the bits above 31 back in (2^31 == 1 mod p), twice at most
+    uint64_t v = (uint64_t)state * 16807ull;
+    v = (v & 0x7FFFFFFFull) + (v >> 31);
+    v = (v & 0x7FFFFFFFull) + (v >> 31);
+    state = (uint32_t)(v == 0x7FFFFFFFull ? 0 : v);
     return state;
 }
 
-void HostIndex::draw_levels(size_t n, std::vector<int16_t>& out) {
+// state after `steps` more draws: x * 16807^steps mod (2^31 - 1)
+static inline uint32_t minstd_skip(uint32_t state, uint64_t steps) {
+    uint64_t base = 16807ull, acc = state;
+    const uint64_t p = 2147483647ull;
+    for (; steps; steps >>= 1) {
+        if (steps & 1)
+            acc = acc * base % p;
+        base = base * base % p;
+    }
+    return (uint32_t)acc;
+}
+
+static void draw_level_range(uint32_t state, uint32_t m, int16_t* out, size_t n) {
     const double inverse_log_connectivity = 1.0 / std::log((double)m);
     const double range = 2147483646.0;
-    out.resize(n);
+    // 1 - 1/m of all draws give level 0: r safely above 1/m needs no logarithm (the margin keeps every r whose
+    // -log(r) / log(m) could round to 1.0 on the exact path)
+    const double level0_above = (1.0 / (double)m) * (1.0 + 1e-9);
     for (size_t i = 0; i < n; ++i) {
-        double low = (double)(minstd_next(level_rng) - 1u);
-        double high = (double)(minstd_next(level_rng) - 1u);
+        double low = (double)(minstd_next(state) - 1u);
+        double high = (double)(minstd_next(state) - 1u);
         double r = (low + high * range) / (range * range);
+        if (r > level0_above && r < 1.0) {
+            out[i] = 0;
+            continue;
+        }
         if (r >= 1.0)
             r = std::nextafter(1.0, 0.0);
         double l = -std::log(r) * inverse_log_connectivity;
@@ -103,6 +125,29 @@ void HostIndex::draw_levels(size_t n, std::vector<int16_t>& out) {
             l = 30.0;  // r == 0 would be +inf; never happens with minstd, keeps the cast defined
         out[i] = (int16_t)l;
     }
+}
+
+void HostIndex::draw_levels(size_t n, std::vector<int16_t>& out) {
+    out.resize(n);
+    // every node consumes exactly two draws, so the stream can be cut anywhere: large requests are split over
+    // threads, each starting from the jumped-ahead state (10 M levels: 110 ms on one core)
+    size_t threads = n >= (1u << 20) ? std::min<size_t>(16, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    if (threads <= 1) {
+        draw_level_range(level_rng, m, out.data(), n);
+    } else {
+        std::vector<std::thread> pool;
+        const size_t per = (n + threads - 1) / threads;
+        for (size_t t = 0; t < threads; ++t) {
+            const size_t lo = std::min(n, t * per), hi = std::min(n, lo + per);
+            if (lo == hi)
+                continue;
+            const uint32_t start = minstd_skip(level_rng, 2 * (uint64_t)lo);
+            pool.emplace_back(draw_level_range, start, m, out.data() + lo, hi - lo);
+        }
+        for (std::thread& th : pool)
+            th.join();
+    }
+    level_rng = minstd_skip(level_rng, 2 * (uint64_t)n);
 }
 
 // ------------------------------------------------------------------------------------------------ accessors
@@ -317,6 +362,24 @@ void HostIndex::note_new_keys(uint64_t const* new_keys, size_t n) {
         if (map_valid_)
             map_keys_.insert(new_keys[i], (uint32_t)(first + i));
     }
+}
+
+void HostIndex::truncate_rows(size_t rows, int32_t old_max_level, uint64_t old_entry) {
+    keys.resize(rows);
+    levels.resize(rows);
+    upper_off.resize(rows + 1);
+    max_level = old_max_level;
+    entry = old_entry;
+    map_keys_.clear();
+    map_valid_ = false;
+    keys_ascending_ = true;
+    max_key_ = 0;
+    for (size_t i = 0; i < rows; ++i) {
+        if (i && keys[i] <= max_key_)
+            keys_ascending_ = false;
+        max_key_ = std::max(max_key_, keys[i]);
+    }
+    stats_cache_size_ = (size_t)-1;
 }
 
 // ------------------------------------------------------------------------------------------------ file format

@@ -99,6 +99,8 @@ class HostIndex {
     // returns the offending key's position or -1 when every new key is unique and absent
     int64_t check_new_keys(uint64_t const* new_keys, size_t n);
     void note_new_keys(uint64_t const* new_keys, size_t n);
+    // undo an append that was committed before the device confirmed it: keep the first `rows` nodes
+    void truncate_rows(size_t rows, int32_t old_max_level, uint64_t old_entry);
 
     // serialisation; `vectors` may be null only when exclude_vectors
     std::string save(char const* path, uint8_t const* vectors, bool exclude_vectors) const;
