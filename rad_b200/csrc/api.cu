@@ -70,6 +70,7 @@ struct DeviceState {
     uint32_t* upper_off = nullptr;
     int8_t* levels = nullptr;
     uint32_t* task_rel = nullptr;
+    uint32_t* task_order = nullptr;  // per slot: the t-th unit of work of a batch is node batch_start + task_order[batch_start + t]
     size_t cap_rows = 0, cap_upper = 0;
     size_t rows = 0, upper_rows = 0;  // what the device currently holds
     // per-batch scratch
@@ -99,6 +100,7 @@ struct DeviceState {
         cudaFree(upper_off);
         cudaFree(levels);
         cudaFree(task_rel);
+        cudaFree(task_order);
         for (int i = 0; i < 2; ++i) {
             cudaFree(pair_keys[i]);
             cudaFree(pair_vals[i]);
@@ -185,6 +187,7 @@ std::string ensure_capacity(rb_index* ix, size_t rows, size_t upper) {
         if (!(err = grow_array(d.upper_off, d.cap_rows, cap, 0, d.stream)).empty()) return err;
         if (!(err = grow_array(d.levels, d.cap_rows, cap, 0, d.stream)).empty()) return err;
         if (!(err = grow_array(d.task_rel, d.cap_rows, cap, 0, d.stream)).empty()) return err;
+        if (!(err = grow_array(d.task_order, d.cap_rows, cap, 0, d.stream)).empty()) return err;
         d.cap_rows = cap;
     }
     if (upper > d.cap_upper) {
@@ -282,11 +285,12 @@ struct Batch {
 // The schedule is a pure function of (current size, levels): mirrored by tests/model/batched_model.c.
 void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all_levels /* old + new */,
                   std::vector<Batch>& batches, std::vector<uint32_t>& task_rel /* per new node */,
-                  int32_t& max_level, uint64_t& entry) {
+                  std::vector<uint32_t>& task_order /* per new node */, int32_t& max_level, uint64_t& entry) {
     const size_t total = all_levels.size();
     const uint32_t den = ix->opts.batch_growth_den, bmax = ix->opts.batch_max;
     size_t s = old_size;
     task_rel.assign(total - old_size, 0);
+    task_order.assign(total - old_size, 0);
     while (s < total) {
         if (ix->opts.debug_max_batches && batches.size() >= ix->opts.debug_max_batches)
             break;
@@ -316,6 +320,23 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
         for (size_t t = 0; t < b; ++t) {
             task_rel[s + t - old_size] = tasks;
             tasks += (uint32_t)(std::min<int32_t>(all_levels[s + t], max_level) + 1);
+        }
+        // order of work inside the batch: nodes with more levels to search first (longest job first), so the last
+        // wave of a launch holds only the short level-0 jobs; the nodes are independent, so any order gives the
+        // same graph.  Stable counting sort by the number of searched levels, descending.
+        {
+            size_t count[65] = {0};
+            auto jobs = [&](size_t t) { return (size_t)std::min<int32_t>(all_levels[s + t], max_level); };
+            for (size_t t = 0; t < b; ++t)
+                ++count[std::min<size_t>(jobs(t), 63)];
+            size_t start[65];
+            size_t acc = 0;
+            for (int l = 63; l >= 0; --l) {
+                start[l] = acc;
+                acc += count[l];
+            }
+            for (size_t t = 0; t < b; ++t)
+                task_order[s - old_size + start[std::min<size_t>(jobs(t), 63)]++] = (uint32_t)t;
         }
         batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, tasks});
         for (size_t t = 0; t < b; ++t)
@@ -407,10 +428,10 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     std::vector<int16_t> all_levels(h.levels);
     all_levels.insert(all_levels.end(), new_levels.begin(), new_levels.end());
     std::vector<Batch> batches;
-    std::vector<uint32_t> task_rel;
+    std::vector<uint32_t> task_rel, task_order;
     int32_t max_level = h.max_level;
     uint64_t entry = h.entry;
-    plan_batches(ix, old_size, all_levels, batches, task_rel, max_level, entry);
+    plan_batches(ix, old_size, all_levels, batches, task_rel, task_order, max_level, entry);
 
     // per-node metadata of the new rows
     std::vector<uint32_t> off32(n);
@@ -424,6 +445,7 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     RB_CUDA(cudaMemcpyAsync(d.upper_off + old_size, off32.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
     RB_CUDA(cudaMemcpyAsync(d.levels + old_size, lv8.data(), n, cudaMemcpyHostToDevice, d.stream));
     RB_CUDA(cudaMemcpyAsync(d.task_rel + old_size, task_rel.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
+    RB_CUDA(cudaMemcpyAsync(d.task_order + old_size, task_order.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
 
     // scratch sized for the largest batch
     size_t max_pairs = 0;
@@ -483,6 +505,7 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
             ip.g = g;
             ip.levels = d.levels;
             ip.task_rel = d.task_rel;
+            ip.order = d.task_order + b.start;
             ip.pair_keys = d.pair_keys[0];
             ip.pair_vals = d.pair_vals[0];
             ip.batch_start = b.start;

@@ -575,6 +575,7 @@ struct InsertParams {
     uint32_t bloom_log2;
     unsigned int* work_counter;
     unsigned long long* counters;  // [0] distances, [1] expansions
+    const uint32_t* order;         // the t-th unit of work of the batch is node batch_start + order[t]
 };
 
 // MINB = resident CTAs per SM the register budget is sized for: 4 (<= 128 registers, 8 loads in flight per lane) when
@@ -593,7 +594,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_kernel(Inser
         t = __shfl_sync(RB_FULL_MASK, t, 0);
         if (t >= p.batch_size)
             break;
-        const uint32_t slot = p.batch_start + t;
+        const uint32_t slot = p.batch_start + __ldg(p.order + t);
         const uint4 q4 = load_slice(p.g.fp, slot, sub);
         const int lq = p.levels[slot];
         uint32_t cur = p.entry;
