@@ -510,8 +510,12 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
 // ------------------------------------------------------------------------------------------------ selection heuristic
 // index.hpp:4246-4289 over `count` ascending keys in shared memory `cand`; writes the selected keys to w.sel and
 // returns how many (<= needed <= kMaxWidth).  Keys keep their low (expanded) bit; callers mask it.
+// `q4` is the slice (lane & 7) of the fingerprint the candidates' keys were measured from: the test
+// d(c, s) < d(c, q) is done on the integer counts, i_cs * u_cq > i_cq * u_cs, which is the same decision as comparing
+// the order keys (they are strictly monotone in i / u and equal for equal ratios) without a divide per pair.
 __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, const WarpScratch& w, const uint64_t* cand,
-                                                          uint32_t count, uint32_t needed, TraversalCounters& tc) {
+                                                          uint32_t count, uint32_t needed, TraversalCounters& tc,
+                                                          uint4 q4) {
     const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
     if (count < needed) {
         for (uint32_t i = lane; i < count; i += 32)
@@ -533,14 +537,15 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
         uint32_t ci = c + grp;  // each group of 8 lanes examines one candidate
         bool have = ci < count;
         uint64_t ck = have ? cand[ci] : 0ull;
-        uint32_t cbits = key_bits(ck);
         uint4 a = have ? load_slice(g.fp, key_slot(ck), sub) : make_uint4(0, 0, 0, 0);
         bool good = have;
+        const uint32_t vq = group8_inter_union(a, q4);
+        const uint32_t icq = vq & 0xFFFFu, ucq = (vq >> 16) ? (vq >> 16) : 1u;  // u == 0: ratio 0
         for (uint32_t j = 0; j < kept; ++j) {
             uint4 s = w.kept[j * 8 + sub];
             uint32_t v = group8_inter_union(a, s);
-            uint32_t between = order_key_bits(v & 0xFFFFu, v >> 16);
-            good = good && !(between < cbits);
+            const uint32_t ics = v & 0xFFFFu, ucs = (v >> 16) ? (v >> 16) : 1u;
+            good = good && !(ics * ucq > icq * ucs);  // counts <= 1024, unions <= 2048: no overflow
         }
         tc.distances += kept * (count - c < 4 ? count - c : 4);
         uint32_t gm = __ballot_sync(RB_FULL_MASK, good && sub == 0);  // bit 8*grp set when that candidate passes
@@ -604,7 +609,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_kernel(Inser
         uint32_t task = p.task_rel[slot];
         for (int level = lq < p.max_level ? lq : p.max_level; level >= 0; --level, ++task) {
             uint32_t len = warp_beam_search(p.g, w, q4, cur, cur_bits, level, p.ef, tc);
-            uint32_t ns = warp_select_neighbors(p.g, w, w.list, len, p.g.m, tc);
+            uint32_t ns = warp_select_neighbors(p.g, w, w.list, len, p.g.m, tc, q4);
             uint32_t width;
             uint32_t* mine = graph_row(p.g, slot, level, width);
             uint64_t sk = (uint32_t)lane < ns ? w.sel[lane] : 0ull;
@@ -747,8 +752,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(Rever
             cand[deg + lane + 32] = ((inc[lane + 32] >> 32) << 32) | ((uint64_t)(uint32_t)inc[lane + 32] << 1);
     }
     // distances from the target to its current neighbours
+    const uint4 t4 = load_slice(p.g.fp, target, sub);
     {
-        uint4 t4 = load_slice(p.g.fp, target, sub);
         uint32_t bits = warp_eval(p.g.fp, t4, have, deg);
         tc.distances += deg;
         if ((uint32_t)lane < deg)
@@ -763,7 +768,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(Rever
     cand[lane] = a;
     cand[lane + 32] = b;
     __syncwarp();
-    uint32_t ns = warp_select_neighbors(p.g, w, cand, nc, width, tc);
+    uint32_t ns = warp_select_neighbors(p.g, w, cand, nc, width, tc, t4);
     if ((uint32_t)lane < width)
         row[lane] = (uint32_t)lane < ns ? key_slot(w.sel[lane]) : RB_EMPTY;
     if (lane == 0)
