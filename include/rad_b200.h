@@ -150,6 +150,14 @@ RB_EXPORT void rb_metadata(char const* path, rb_metadata_t* out, rb_error_t* err
  * number of u64 written (2 x neighbours).  Out-of-range slot/level sets *error (-> ValueError). */
 RB_EXPORT size_t rb_neighbors(rb_index_t const* index, size_t slot, int level, uint64_t* out_pairs, size_t capacity,
                               rb_error_t* error);
+/* Batched form (additive): neighbours of `count` (slot, level) pairs in one call, for a service
+ * that prefetches the lists of many work items per round trip (rad/coordination_service.py:308-328 asks one node at
+ * a time through a queue).  Lists are written back to back as [slot, key, ...]; offsets[i] .. offsets[i + 1] is the
+ * u64 range of request i (offsets has count + 1 entries).  levels == NULL means level 0 for every slot.  An
+ * out-of-range request yields an EMPTY list (offsets[i + 1] == offsets[i]) and is counted in the return value, the
+ * number of failed requests; *error is set only when `capacity` is too small (2 x 2 x connectivity x count suffices). */
+RB_EXPORT size_t rb_neighbors_many(rb_index_t const* index, uint64_t const* slots, int32_t const* levels, size_t count,
+                                   uint64_t* out_pairs, size_t capacity, uint64_t* offsets, rb_error_t* error);
 /* with out_pairs == NULL returns the required capacity (2 x nodes on the top level) */
 RB_EXPORT size_t rb_top_level_nodes(rb_index_t const* index, uint64_t* out_pairs, size_t capacity, rb_error_t* error);
 RB_EXPORT void rb_keys_from_slots(rb_index_t const* index, uint64_t const* slots, size_t count, uint64_t* keys_out,

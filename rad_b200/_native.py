@@ -86,6 +86,8 @@ SIGNATURES = {
     "rb_view": (None, [_H, C.c_char_p, C.c_int, _ERR]),
     "rb_metadata": (None, [C.c_char_p, C.POINTER(Metadata), _ERR]),
     "rb_neighbors": (C.c_size_t, [_H, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, _ERR]),
+    "rb_neighbors_many": (C.c_size_t, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p,
+                                       _ERR]),
     "rb_top_level_nodes": (C.c_size_t, [_H, C.c_void_p, C.c_size_t, _ERR]),
     "rb_keys_from_slots": (None, [_H, C.c_void_p, C.c_size_t, C.c_void_p, _ERR]),
     "rb_slots_from_keys": (None, [_H, C.c_void_p, C.c_size_t, C.c_void_p, _ERR]),

@@ -1370,6 +1370,36 @@ size_t rb_neighbors(rb_index_t const* ix, size_t slot, int level, uint64_t* out_
     return written;
 }
 
+size_t rb_neighbors_many(rb_index_t const* ix, uint64_t const* slots, int32_t const* levels, size_t count,
+                         uint64_t* out_pairs, size_t capacity, uint64_t* offsets, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!ix->host_graph_valid) {
+        set_error(error, "the host copy of the graph is stale: call rb_sync_host first");
+        return 0;
+    }
+    size_t written = 0, failed = 0;
+    offsets[0] = 0;
+    uint32_t tmp[64];
+    for (size_t i = 0; i < count; ++i) {
+        int cnt = ix->host.neighbors((size_t)slots[i], levels ? (int)levels[i] : 0, tmp, 64);
+        if (cnt < 0) {
+            ++failed;
+            cnt = 0;
+        }
+        if (written + 2 * (size_t)cnt > capacity) {
+            set_error(error, "output capacity too small for rb_neighbors_many");
+            return failed;
+        }
+        for (int j = 0; j < cnt; ++j) {
+            out_pairs[written++] = tmp[j];
+            out_pairs[written++] = ix->host.key_of(tmp[j]);
+        }
+        offsets[i + 1] = written;
+    }
+    return failed;
+}
+
 size_t rb_top_level_nodes(rb_index_t const* ix, uint64_t* out_pairs, size_t capacity, rb_error_t* error) {
     if (error)
         *error = nullptr;

@@ -350,6 +350,23 @@ class Index:
         self._check(err)
         return out[:n].copy()
 
+    def get_neighbors_many(self, node_ids, levels=None):
+        """Neighbour lists of many (node_id, level) pairs in one call (additive API).
+
+        Returns ``(pairs, offsets)``: ``pairs[offsets[i]:offsets[i + 1]]`` is the ``[slot, key, ...]`` list of request
+        ``i``, exactly what ``get_neighbors(node_ids[i], levels[i])`` returns; an out-of-range request gives an empty
+        list instead of raising.  ``levels=None`` means level 0 for every node."""
+        ids = np.ascontiguousarray(np.asarray(node_ids).astype(np.uint64).reshape(-1))
+        lv = None if levels is None else np.ascontiguousarray(
+            np.broadcast_to(np.asarray(levels, dtype=np.int32), ids.shape))
+        out = np.empty(max(1, 4 * int(self.connectivity) * len(ids)), dtype=np.uint64)
+        offsets = np.zeros(len(ids) + 1, dtype=np.uint64)
+        err = C.c_char_p()
+        self._lib.rb_neighbors_many(self._handle(), ids.ctypes.data, None if lv is None else lv.ctypes.data, len(ids),
+                                    out.ctypes.data, out.size, offsets.ctypes.data, C.byref(err))
+        self._check(err)
+        return out[:int(offsets[-1])].copy(), offsets.astype(np.int64)
+
     def get_top_level_nodes(self):
         """``[slot, key, ...]`` of every node on the top level (lib.cpp:290-305)."""
         err = C.c_char_p()

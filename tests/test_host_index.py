@@ -119,3 +119,27 @@ def test_reads_survive_fork(native, golden_dir):
     nb, top, n, ml = q.get(timeout=30)
     p.join(30)
     assert nb == g["nb_0_0"].tolist() and top == g["top_level_nodes"].tolist() and n == 1000 and ml == int(g["max_level"])
+
+
+def test_batched_neighbour_reads_equal_single_reads(native, golden_dir):
+    """rb_neighbors_many (additive API): every list equals the single-call answer; out-of-range
+    requests come back empty instead of raising."""
+    import os
+
+    import numpy as np
+
+    from rad_b200.index import Index
+    ix = Index(path=os.path.join(golden_dir, "ref_n1000_m8.usearch"), view=True, exclude_vectors=True)
+    gold = np.load(os.path.join(golden_dir, "ref_n1000_m8.npz"))
+    levels = gold["levels"]
+    slots = np.arange(len(levels))
+    pairs, off = ix.get_neighbors_many(slots)
+    assert len(off) == len(slots) + 1 and off[0] == 0
+    for s in range(0, len(slots), 11):
+        assert (pairs[off[s]:off[s + 1]] == ix.get_neighbors(int(s), 0)).all()
+    upper = np.nonzero(levels > 0)[0]
+    pairs, off = ix.get_neighbors_many(upper, levels[upper])
+    for i, s in enumerate(upper):
+        assert (pairs[off[i]:off[i + 1]] == ix.get_neighbors(int(s), int(levels[s]))).all()
+    pairs, off = ix.get_neighbors_many([0, len(levels) + 7, 1], [0, 0, 99])
+    assert off[1] > 0 and off[2] == off[1] and off[3] == off[2]
