@@ -8,10 +8,12 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
@@ -51,6 +53,20 @@ std::string format(char const* fmt, ...) {
             return format("CUDA error %s at %s:%d (%s)", cudaGetErrorName(e_), __FILE__, __LINE__,      \
                           cudaGetErrorString(e_));                                                      \
     } while (0)
+
+// RB_HOST_TIMING=1 prints the host-side phases of an add to stderr (tuning aid)
+struct PhaseTimer {
+    bool on = std::getenv("RB_HOST_TIMING") != nullptr;
+    std::chrono::steady_clock::time_point last = std::chrono::steady_clock::now();
+    void mark(char const* what) {
+        if (!on)
+            return;
+        auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[rb host] %-28s %8.2f ms\n", what,
+                     std::chrono::duration<double, std::milli>(now - last).count());
+        last = now;
+    }
+};
 
 size_t ceil2(size_t v) {
     size_t r = 1;
@@ -282,6 +298,26 @@ struct Batch {
     uint32_t tasks;
 };
 
+// run f(i) for i in [0, count) on up to 16 host threads (static interleaved split; f must be thread-safe per i)
+template <typename F>
+void parallel_for(size_t count, size_t min_per_thread, F&& f) {
+    size_t threads = std::min<size_t>({16, std::max(1u, std::thread::hardware_concurrency()),
+                                       std::max<size_t>(1, count / std::max<size_t>(1, min_per_thread))});
+    if (threads <= 1) {
+        for (size_t i = 0; i < count; ++i)
+            f(i);
+        return;
+    }
+    std::vector<std::thread> pool;
+    for (size_t t = 0; t < threads; ++t)
+        pool.emplace_back([&, t]() {
+            for (size_t i = t; i < count; i += threads)
+                f(i);
+        });
+    for (std::thread& th : pool)
+        th.join();
+}
+
 // The schedule is a pure function of (current size, levels): mirrored by tests/model/batched_model.c.
 void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all_levels /* old + new */,
                   std::vector<Batch>& batches, std::vector<uint32_t>& task_rel /* per new node */,
@@ -291,6 +327,7 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
     size_t s = old_size;
     task_rel.assign(total - old_size, 0);
     task_order.assign(total - old_size, 0);
+    // pass 1 (sequential, cheap): batch boundaries, and the entry point / top level each batch starts from
     while (s < total) {
         if (ix->opts.debug_max_batches && batches.size() >= ix->opts.debug_max_batches)
             break;
@@ -316,36 +353,45 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
                 run_max = all_levels[s + t];
             }
         }
-        uint32_t tasks = 0;
-        for (size_t t = 0; t < b; ++t) {
-            task_rel[s + t - old_size] = tasks;
-            tasks += (uint32_t)(std::min<int32_t>(all_levels[s + t], max_level) + 1);
-        }
-        // order of work inside the batch: nodes with more levels to search first (longest job first), so the last
-        // wave of a launch holds only the short level-0 jobs; the nodes are independent, so any order gives the
-        // same graph.  Stable counting sort by the number of searched levels, descending.
-        {
-            size_t count[65] = {0};
-            auto jobs = [&](size_t t) { return (size_t)std::min<int32_t>(all_levels[s + t], max_level); };
+        batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, 0});
+        if (raised)
             for (size_t t = 0; t < b; ++t)
-                ++count[std::min<size_t>(jobs(t), 63)];
-            size_t start[65];
-            size_t acc = 0;
-            for (int l = 63; l >= 0; --l) {
-                start[l] = acc;
-                acc += count[l];
-            }
-            for (size_t t = 0; t < b; ++t)
-                task_order[s - old_size + start[std::min<size_t>(jobs(t), 63)]++] = (uint32_t)t;
-        }
-        batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, tasks});
-        for (size_t t = 0; t < b; ++t)
-            if (all_levels[s + t] > max_level) {
-                max_level = all_levels[s + t];
-                entry = s + t;
-            }
+                if (all_levels[s + t] > max_level) {
+                    max_level = all_levels[s + t];
+                    entry = s + t;
+                }
         s += b;
     }
+    // pass 2 (one batch per task, on host threads): first task of every node, and the order of work inside the
+    // batch -- nodes with more levels to search first (longest job first), so the last wave of a launch holds only
+    // the short level-0 jobs; the nodes are independent, so any order gives the same graph.  Stable counting sort
+    // by the number of searched levels, descending.
+    parallel_for(batches.size(), 4, [&](size_t bi) {
+        Batch& bt = batches[bi];
+        if (bt.max_level < 0)
+            return;
+        const size_t s0 = bt.start, b = bt.size;
+        const int32_t top = bt.max_level;
+        uint32_t tasks = 0;
+        size_t count[64] = {0};
+        for (size_t t = 0; t < b; ++t) {
+            const size_t jobs = (size_t)std::min<int32_t>(all_levels[s0 + t], top);
+            task_rel[s0 + t - old_size] = tasks;
+            tasks += (uint32_t)jobs + 1;
+            ++count[std::min<size_t>(jobs, 63)];
+        }
+        bt.tasks = tasks;
+        size_t start[64];
+        size_t acc = 0;
+        for (int l = 63; l >= 0; --l) {
+            start[l] = acc;
+            acc += count[l];
+        }
+        for (size_t t = 0; t < b; ++t) {
+            const size_t jobs = (size_t)std::min<int32_t>(all_levels[s0 + t], top);
+            task_order[s0 - old_size + start[std::min<size_t>(jobs, 63)]++] = (uint32_t)t;
+        }
+    });
 }
 
 // resident CTAs per SM that `smem` bytes of dynamic shared memory per CTA allow, quantised to the compiled variants
@@ -431,7 +477,9 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     std::vector<uint32_t> task_rel, task_order;
     int32_t max_level = h.max_level;
     uint64_t entry = h.entry;
+    PhaseTimer pt;
     plan_batches(ix, old_size, all_levels, batches, task_rel, task_order, max_level, entry);
+    pt.mark("  plan_batches");
 
     // per-node metadata of the new rows
     std::vector<uint32_t> off32(n);
@@ -439,9 +487,12 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     uint64_t upper = h.upper_off[old_size];
     for (size_t i = 0; i < n; ++i) {
         off32[i] = (uint32_t)upper;
-        lv8[i] = (int8_t)new_levels[i];
         upper += (uint64_t)new_levels[i];
     }
+    parallel_for((n + 65535) / 65536, 8, [&](size_t c) {
+        for (size_t i = c * 65536, e = std::min(n, i + 65536); i < e; ++i)
+            lv8[i] = (int8_t)new_levels[i];
+    });
     RB_CUDA(cudaMemcpyAsync(d.upper_off + old_size, off32.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
     RB_CUDA(cudaMemcpyAsync(d.levels + old_size, lv8.data(), n, cudaMemcpyHostToDevice, d.stream));
     RB_CUDA(cudaMemcpyAsync(d.task_rel + old_size, task_rel.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
@@ -497,6 +548,7 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         ticks.push_back(ev);
         return cudaEventRecord(ev, d.stream);
     };
+    pt.mark("  metadata uploads + scratch");
     RB_CUDA(cudaEventRecord(d.ev_begin, d.stream));
     for (size_t bi = 0; bi < batches.size(); ++bi) {
         Batch const& b = batches[bi];
@@ -587,8 +639,10 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         h.note_new_keys(keys, count);
     };
     const bool early = !progress && !cancelled && inserted == n;
+    pt.mark("  launch loop");
     if (early)
         commit(n);
+    pt.mark("  commit (device busy)");
     {
         cudaError_t e = cudaStreamSynchronize(d.stream);
         if (e == cudaSuccess)
@@ -605,6 +659,7 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     }
     for (cudaEvent_t ev : marks)
         cudaEventDestroy(ev);
+    pt.mark("  wait for the device");
     RB_CUDA(cudaGetLastError());
     float ms = 0;
     RB_CUDA(cudaEventElapsedTime(&ms, d.ev_begin, d.ev_end));
@@ -662,8 +717,10 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
             generated[i] = old_size + i;
         keys = generated.data();
     }
+    PhaseTimer pt;
     if (h.check_new_keys(keys, n) >= 0)
         return "Duplicate keys not allowed in high-level wrappers";
+    pt.mark("keys generated + checked");
     std::string err = ensure_device(ix);
     if (!err.empty())
         return err;
@@ -672,6 +729,7 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
     std::vector<int16_t> new_levels;
     const uint32_t rng_before = h.level_rng;
     h.draw_levels(n, new_levels);
+    pt.mark("device ready + level stream");
     uint64_t upper = h.upper_off[old_size];
     for (size_t i = 0; i < n; ++i)
         upper += (uint64_t)new_levels[i];
@@ -692,7 +750,9 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
         RB_CUDA(cudaMemsetAsync(d.adju + h.upper_off[old_size] * h.m, 0xFF,
                                 (upper - h.upper_off[old_size]) * (size_t)h.m * 4, d.stream));
     size_t accepted = 0;
+    pt.mark("capacity + copies enqueued");
     err = build_new_rows(ix, keys, n, new_levels, progress, user, accepted);
+    pt.mark("build_new_rows");
     if (accepted < n) {
         // the level stream only advances over nodes that exist
         h.level_rng = rng_before;
