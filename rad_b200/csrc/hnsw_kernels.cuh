@@ -418,20 +418,38 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         uint64_t key2 = both ? w.list[pos2] : ~0ull;
         uint32_t src1 = 32, src2 = 33;  // 32/33 = list entry pos1/pos2, < 32 = pending lane
         if (pn) {
-            // pending keys below the last scanned entry compete for the two places (pn > 0 implies a full scan)
-            uint32_t cand = __ballot_sync(RB_FULL_MASK, !(pk & 1ull) && pk < (two ? key2 : key1));
-            while (cand) {
-                int l = __ffs((int)cand) - 1;
-                cand &= cand - 1;
-                uint64_t x = __shfl_sync(RB_FULL_MASK, pk, l);
-                if (x < key1) {
-                    key2 = key1;
-                    src2 = src1;
-                    key1 = x;
-                    src1 = (uint32_t)l;
-                } else if (x < key2) {
-                    key2 = x;
-                    src2 = (uint32_t)l;
+            // pending keys below the last scanned entry compete for the two places (pn > 0 implies a full scan):
+            // the two smallest of them by warp-wide minimum (REDUX on the high word, then on the low word among
+            // its holders; keys are unique), then a 2 + 2 merge with the list entries
+            const bool comp = !(pk & 1ull) && pk < (two ? key2 : key1);
+            if (__ballot_sync(RB_FULL_MASK, comp)) {
+                const uint32_t hi = (uint32_t)(pk >> 32), lo = (uint32_t)pk;
+                uint32_t mh = __reduce_min_sync(RB_FULL_MASK, comp ? hi : 0xFFFFFFFFu);
+                uint32_t ml = __reduce_min_sync(RB_FULL_MASK, (comp && hi == mh) ? lo : 0xFFFFFFFFu);
+                const uint32_t l1 = (uint32_t)__ffs((int)__ballot_sync(RB_FULL_MASK, comp && hi == mh && lo == ml)) - 1;
+                const uint64_t x1 = ((uint64_t)mh << 32) | ml;
+                uint64_t x2 = ~0ull;
+                uint32_t l2 = 0;
+                const bool comp2 = comp && (uint32_t)lane != l1;
+                if (two && __ballot_sync(RB_FULL_MASK, comp2)) {
+                    mh = __reduce_min_sync(RB_FULL_MASK, comp2 ? hi : 0xFFFFFFFFu);
+                    ml = __reduce_min_sync(RB_FULL_MASK, (comp2 && hi == mh) ? lo : 0xFFFFFFFFu);
+                    l2 = (uint32_t)__ffs((int)__ballot_sync(RB_FULL_MASK, comp2 && hi == mh && lo == ml)) - 1;
+                    x2 = ((uint64_t)mh << 32) | ml;
+                }
+                if (x1 < key1) {
+                    if (x2 < key1) {
+                        key2 = x2;
+                        src2 = l2;
+                    } else {
+                        key2 = key1;
+                        src2 = src1;
+                    }
+                    key1 = x1;
+                    src1 = l1;
+                } else {  // key1 < x1 < key2
+                    key2 = x1;
+                    src2 = l1;
                 }
             }
         }
