@@ -190,3 +190,72 @@ def test_fork_safe_graph_reads():
     nb, top, size, ml = qout.get(timeout=60)
     p.join(30)
     assert nb == want.tolist() and size == 2000 and ml == ix.max_level and top == ix.get_top_level_nodes().tolist()
+
+
+def test_full_size_build_properties():
+    """BASELINE.json configs[1] at its full size (10 M x 1024 bit, M=8, ef_add=400), through size-independent
+    properties: structure of the whole graph (vectorised), level population, and the answers of the ef-bounded search
+    against the exact search on the same device-resident rows (exact answers are themselves pinned bit for bit at
+    small sizes, and by properties at 2 M x 512, in tests/test_gpu_exact.py)."""
+    import ctypes as C
+
+    import torch
+
+    from rad_b200 import _native
+    n, m, k = 10_000_000, 8, 10
+    L = _native.lib()
+    err = C.c_char_p()
+    centres = synth.centre_table(0, n)
+    d_c = torch.from_numpy(centres).cuda()
+    d_db = torch.empty((n, 128), dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    L.rb_synth_fingerprints_device(d_db.data_ptr(), 0, n, 0, d_c.data_ptr(), len(centres), 1, stream, C.byref(err))
+    _native.check(err)
+    torch.cuda.synchronize()
+    ix = Index(ndim=1024, connectivity=m, expansion_add=400, expansion_search=128)
+    L.rb_add_device(ix._handle(), None, d_db.data_ptr(), n, C.byref(err))
+    _native.check(err)
+    assert len(ix) == n
+    lv = ix.levels
+    adj0, adju = ix._debug_adjacency()
+    # level population follows P(level >= l) = M^-l (the reference's level stream, index.hpp:3867-3871)
+    for l in (1, 2, 3):
+        frac = float((lv >= l).mean())
+        assert abs(frac - m ** -l) < 0.05 * m ** -l, (l, frac)
+    assert int(lv[ix.entry_slot]) == ix.max_level == int(lv.max())
+    # level 0: ids in range, rows packed at the front, no self loops, no duplicates, nobody isolated
+    valid = adj0 != EMPTY
+    cnt = valid.sum(axis=1)
+    assert cnt.min() >= 1 and cnt.max() <= 2 * m
+    assert (valid == (np.arange(2 * m)[None, :] < cnt[:, None])).all()
+    assert (adj0[valid] < n).all()
+    assert not (adj0 == np.arange(n, dtype=np.uint32)[:, None]).any()
+    srt = np.sort(adj0, axis=1)
+    assert not ((srt[:, 1:] == srt[:, :-1]) & (srt[:, 1:] != EMPTY)).any()
+    # upper levels: a link on level l only goes to a node that exists on level l
+    upper_off = np.concatenate([[0], np.cumsum(lv.astype(np.int64))])
+    owner = np.repeat(np.arange(n), lv.astype(np.int64))
+    row_level = np.arange(len(owner)) - upper_off[owner] + 1
+    uv = adju != EMPTY
+    assert (adju[uv] < n).all()
+    assert (lv[adju[uv]] >= np.broadcast_to(row_level[:, None], adju.shape)[uv]).all()
+    assert not (adju == owner[:, None].astype(np.uint32)).any()
+    # search: answers ascending with reference-exact distances; recall against the exact search is what this generator
+    # gives at this size for either implementation (0.47 at ef=128, and as many queries find themselves: N/100 nearly
+    # orthogonal centres leave greedy routing no gradient between clusters -- DESIGN.md §9), far above chance
+    nq = 2000
+    pick = torch.arange(nq, device="cuda") * (n // nq)
+    d_q = d_db[pick].contiguous()
+    q = d_q.cpu().numpy()
+    res = ix.search(q, k)
+    assert (res.counts == k).all()
+    assert (np.diff(res.distances, axis=1) >= 0).all()
+    fp = d_db[torch.from_numpy(res.keys.astype(np.int64)).cuda().reshape(-1)].cpu().numpy().reshape(nq, k, 128)
+    inter = np.unpackbits(fp & q[:, None, :], axis=2).sum(axis=2).astype(np.float64)
+    union = np.unpackbits(fp | q[:, None, :], axis=2).sum(axis=2).astype(np.float64)
+    want = np.where(union > 0, 1.0 - inter / np.maximum(union, 1), 1.0).astype(np.float32)
+    assert np.array_equal(res.distances.view(np.uint32), want.view(np.uint32))
+    assert (res.distances[:, 0] == 0).mean() > 0.40
+    exact = ix.search(q, k, exact=True)
+    assert (exact.distances[:, 0] == 0).all()
+    assert _recall(res.distances, exact.distances, k) > 0.40
