@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librad_b200.so")
+# RAD_B200_LIB: development aid for A/B timing of two builds of the SAME library (never a different implementation)
+LIB_PATH = os.environ.get("RAD_B200_LIB") or os.path.join(_HERE, "librad_b200.so")
 
 
 class InitOptions(C.Structure):

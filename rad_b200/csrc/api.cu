@@ -84,6 +84,8 @@ struct DeviceState {
     uint32_t* adj0 = nullptr;
     uint32_t* adju = nullptr;
     uint32_t* upper_off = nullptr;
+    uint16_t* pc0 = nullptr;  // link popcounts mirroring adj0 / adju (device_common.cuh)
+    uint16_t* pcu = nullptr;
     int8_t* levels = nullptr;
     uint32_t* task_rel = nullptr;
     uint32_t* task_order = nullptr;  // per slot: the t-th unit of work of a batch is node batch_start + task_order[batch_start + t]
@@ -114,6 +116,8 @@ struct DeviceState {
         cudaFree(adj0);
         cudaFree(adju);
         cudaFree(upper_off);
+        cudaFree(pc0);
+        cudaFree(pcu);
         cudaFree(levels);
         cudaFree(task_rel);
         cudaFree(task_order);
@@ -201,6 +205,7 @@ std::string ensure_capacity(rb_index* ix, size_t rows, size_t upper) {
         if (!(err = grow_array(d.fp, d.cap_rows * 8, cap * 8, 0, d.stream)).empty()) return err;
         if (!(err = grow_array(d.adj0, d.cap_rows * m0, cap * m0, 0xFF, d.stream)).empty()) return err;
         if (!(err = grow_array(d.upper_off, d.cap_rows, cap, 0, d.stream)).empty()) return err;
+        if (!(err = grow_array(d.pc0, d.cap_rows * m0, cap * m0, 0, d.stream)).empty()) return err;
         if (!(err = grow_array(d.levels, d.cap_rows, cap, 0, d.stream)).empty()) return err;
         if (!(err = grow_array(d.task_rel, d.cap_rows, cap, 0, d.stream)).empty()) return err;
         if (!(err = grow_array(d.task_order, d.cap_rows, cap, 0, d.stream)).empty()) return err;
@@ -210,6 +215,7 @@ std::string ensure_capacity(rb_index* ix, size_t rows, size_t upper) {
         size_t cap = std::max(ceil2(upper), (size_t)1024);
         std::string err = grow_array(d.adju, d.cap_upper * m, cap * m, 0xFF, d.stream);
         if (!err.empty()) return err;
+        if (!(err = grow_array(d.pcu, d.cap_upper * m, cap * m, 0, d.stream)).empty()) return err;
         d.cap_upper = cap;
     }
     ix->host.capacity = std::max(ix->host.capacity, d.cap_rows);
@@ -258,7 +264,20 @@ std::string upload_graph(rb_index* ix) {
         }
         RB_CUDA(cudaMemcpyAsync(d.upper_off, off32.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
         RB_CUDA(cudaMemcpyAsync(d.levels, lv8.data(), n, cudaMemcpyHostToDevice, d.stream));
-        RB_CUDA(cudaStreamSynchronize(d.stream));
+        // link popcounts of the loaded graph
+        uint16_t* node_pc = nullptr;
+        RB_CUDA(cudaMalloc(&node_pc, n * sizeof(uint16_t)));
+        const unsigned grid = (unsigned)std::min<size_t>((n * 8 + 255) / 256, (size_t)d.sm_count * 16);
+        rb::node_popcount_kernel<<<grid, 256, 0, d.stream>>>(d.fp, (uint32_t)n, node_pc);
+        rb::link_popcount_kernel<<<(unsigned)d.sm_count * 8, 256, 0, d.stream>>>(d.adj0, n * (size_t)h.m0, node_pc, d.pc0);
+        if (h.upper_off[n])
+            rb::link_popcount_kernel<<<(unsigned)d.sm_count * 8, 256, 0, d.stream>>>(
+                d.adju, h.upper_off[n] * (size_t)h.m, node_pc, d.pcu);
+        cudaError_t le = cudaGetLastError();
+        cudaError_t se = cudaStreamSynchronize(d.stream);
+        cudaFree(node_pc);
+        RB_CUDA(le);
+        RB_CUDA(se);
     }
     d.rows = n;
     d.upper_rows = h.upper_off[n];
@@ -458,6 +477,8 @@ rb::GraphView graph_view(rb_index* ix) {
     g.adj0 = ix->dev.adj0;
     g.adju = ix->dev.adju;
     g.upper_off = ix->dev.upper_off;
+    g.pc0 = ix->dev.pc0;
+    g.pcu = ix->dev.pcu;
     g.m = ix->host.m;
     g.m0 = ix->host.m0;
     return g;

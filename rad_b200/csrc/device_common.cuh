@@ -59,8 +59,15 @@ struct GraphView {
     uint32_t* adj0;             // rows x m0, RB_EMPTY padded
     uint32_t* adju;             // upper rows x m
     const uint32_t* upper_off;  // rows: first upper row of a node (levels 1..level are consecutive)
+    uint16_t* pc0;              // rows x m0: popcount of the fingerprint each adj0 entry points at (device-only side
+    uint16_t* pcu;              // upper rows x m: the same for adju                                  array, see below)
     uint32_t m, m0;
 };
+
+// Link popcounts.  union = |a| + |q| - intersection, so a traversal that knows |a| for every link it follows needs
+// only the AND-POPC half of the Tanimoto counts.  |a| travels WITH the link: pc0 / pcu mirror adj0 / adju entry for
+// entry (2 bytes per link, read by the same lanes in the same instruction slot as the link row: one extra 32-byte
+// sector per expansion instead of one gather per candidate).  Every writer of a link row writes its popcounts.
 
 __device__ __forceinline__ uint32_t* graph_row(const GraphView& g, uint32_t slot, int level, uint32_t& width) {
     if (level == 0) {
@@ -69,6 +76,27 @@ __device__ __forceinline__ uint32_t* graph_row(const GraphView& g, uint32_t slot
     }
     width = g.m;
     return g.adju + ((size_t)__ldg(g.upper_off + slot) + (uint32_t)(level - 1)) * g.m;
+}
+
+// the popcount row that mirrors `row` (a pointer returned by graph_row for the same level)
+__device__ __forceinline__ uint16_t* graph_row_pc(const GraphView& g, const uint32_t* row, int level) {
+    return level == 0 ? g.pc0 + (row - g.adj0) : g.pcu + (row - g.adju);
+}
+
+// Lane j < cnt holds ids_j (cnt <= 32, warp-uniform); returns to lane j the popcount of fingerprint ids_j.
+__device__ __noinline__ uint32_t warp_popcounts(const uint4* __restrict__ fp, uint32_t ids, uint32_t cnt) {
+    const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
+    uint32_t mine = 0;
+#pragma unroll 1
+    for (uint32_t base = 0; base < cnt; base += 4) {
+        uint32_t j = base + grp;
+        uint32_t id = __shfl_sync(RB_FULL_MASK, ids, j & 31);
+        uint32_t v = group8_sum(j < cnt ? popc4(load_slice(fp, id, sub)) : 0u);
+        uint32_t got = __shfl_sync(RB_FULL_MASK, v, (lane & 3) * 8);
+        if ((uint32_t)(lane >> 2) == (base >> 2))
+            mine = got;
+    }
+    return mine;
 }
 
 }  // namespace rb

@@ -37,7 +37,7 @@ struct WarpScratch {
     uint4* kept;       // kept_rows fingerprints for the selection heuristic   } alias the Bloom filter: the filter is
     uint64_t* sel;     // kMaxWidth selected keys                              } dead once a beam search has ended
     uint64_t* pend;    // 32 qualified candidates not yet merged into the list
-    uint32_t* ids;     // 32 staging ids
+    uint2* ids;        // 32 staging (id, link popcount) pairs
     uint32_t bloom_log2;
 };
 
@@ -45,7 +45,7 @@ struct WarpScratch {
 __host__ __device__ inline size_t warp_scratch_bytes(uint32_t ef, uint32_t bloom_log2, uint32_t kept_rows) {
     size_t list = ((size_t)ef * 8 + 15) & ~(size_t)15;
     size_t bloom = ((size_t)1 << bloom_log2) / 8, select = (size_t)kept_rows * 128 + kMaxWidth * 8;
-    return list + (bloom > select ? bloom : select) + 32 * 8 + 32 * 4;
+    return list + (bloom > select ? bloom : select) + 32 * 8 + 32 * 8;
 }
 
 __device__ __forceinline__ WarpScratch carve_scratch(unsigned char* base, uint32_t ef, uint32_t bloom_log2,
@@ -61,7 +61,7 @@ __device__ __forceinline__ WarpScratch carve_scratch(unsigned char* base, uint32
     w.kept = reinterpret_cast<uint4*>(base);
     w.sel = reinterpret_cast<uint64_t*>(base + (size_t)kept_rows * 128);
     base += bloom > select ? bloom : select;
-    w.ids = reinterpret_cast<uint32_t*>(base);
+    w.ids = reinterpret_cast<uint2*>(base);
     w.bloom_log2 = bloom_log2;
     return w;
 }
@@ -100,9 +100,11 @@ __device__ __forceinline__ uint32_t warp_eval(const uint4* __restrict__ fp, uint
 // The per-round partial sums are reduced with a transposing butterfly: after it lane (grp, sub) holds the complete
 // counts of candidate `cand` = sub * 8 + grp (sub < ROUNDS), 3 shuffles for 4 rounds instead of 4 x 3.
 // qa / qb = query slices (lane & 3) and (lane & 3) + 4.  Returns the order key bits of candidate `cand` (0xFFFFFFFF: none).
+// Only the intersection is counted here: lane j holds |ids_j| in `pcs` (it came with the link, GraphView::pc0 / pcu),
+// pq = |query|, union = |ids_j| + |query| - intersection.
 template <int ROUNDS>
 __device__ __forceinline__ uint32_t warp_eval4_n(const uint4* __restrict__ fp, uint4 qa, uint4 qb, uint32_t ids,
-                                                 uint32_t cnt, uint32_t& cand) {
+                                                 uint32_t pcs, uint32_t pq, uint32_t cnt, uint32_t& cand) {
     static_assert(ROUNDS == 1 || ROUNDS == 2 || ROUNDS == 4, "rounds");
     const int lane = threadIdx.x & 31, sub = lane & 3, grp = lane >> 2;
     uint4 a[ROUNDS], b[ROUNDS];
@@ -119,7 +121,7 @@ __device__ __forceinline__ uint32_t warp_eval4_n(const uint4* __restrict__ fp, u
     for (int r = 0; r < ROUNDS; ++r) {
         v[r] = 0;
         if (r == 0 || (uint32_t)(r * 8) < cnt)  // warp-uniform: a round without candidates costs nothing
-            v[r] = (popc4_and(a[r], qa) + popc4_and(b[r], qb)) | ((popc4_or(a[r], qa) + popc4_or(b[r], qb)) << 16);
+            v[r] = popc4_and(a[r], qa) + popc4_and(b[r], qb);
     }
     uint32_t k;
     if (ROUNDS == 4) {
@@ -140,16 +142,17 @@ __device__ __forceinline__ uint32_t warp_eval4_n(const uint4* __restrict__ fp, u
     }
     if (cand >= cnt)
         cand = 0xFFFFFFFFu;
-    return order_key_bits(k & 0xFFFFu, k >> 16);
+    const uint32_t pc = __shfl_sync(RB_FULL_MASK, pcs, cand & 31);
+    return order_key_bits(k, pc + pq - k);
 }
 
 __device__ __forceinline__ uint32_t warp_eval4(const uint4* __restrict__ fp, uint4 qa, uint4 qb, uint32_t ids,
-                                               uint32_t cnt, uint32_t& cand) {
+                                               uint32_t pcs, uint32_t pq, uint32_t cnt, uint32_t& cand) {
     if (cnt <= 8)
-        return warp_eval4_n<1>(fp, qa, qb, ids, cnt, cand);
+        return warp_eval4_n<1>(fp, qa, qb, ids, pcs, pq, cnt, cand);
     if (cnt <= 16)
-        return warp_eval4_n<2>(fp, qa, qb, ids, cnt, cand);
-    return warp_eval4_n<4>(fp, qa, qb, ids, cnt, cand);
+        return warp_eval4_n<2>(fp, qa, qb, ids, pcs, pq, cnt, cand);
+    return warp_eval4_n<4>(fp, qa, qb, ids, pcs, pq, cnt, cand);
 }
 
 // distance of the query to ONE slot, result in every lane
@@ -376,6 +379,9 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
     qa.z = __shfl_sync(RB_FULL_MASK, q4.z, lane & 3), qa.w = __shfl_sync(RB_FULL_MASK, q4.w, lane & 3);
     qb.x = __shfl_sync(RB_FULL_MASK, q4.x, (lane & 3) + 4), qb.y = __shfl_sync(RB_FULL_MASK, q4.y, (lane & 3) + 4);
     qb.z = __shfl_sync(RB_FULL_MASK, q4.z, (lane & 3) + 4), qb.w = __shfl_sync(RB_FULL_MASK, q4.w, (lane & 3) + 4);
+    uint32_t pq = popc4(qa) + popc4(qb);  // |query| in every lane
+    pq += __shfl_xor_sync(RB_FULL_MASK, pq, 1);
+    pq += __shfl_xor_sync(RB_FULL_MASK, pq, 2);
     // rows of at most 16 links are expanded TWO list entries at a time: lanes 0-15 read one row, lanes 16-31 the other
     const uint32_t row_width = level == 0 ? g.m0 : g.m;
     const bool two = row_width <= 16;
@@ -472,7 +478,7 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
             hint = took2 ? pos2 + 1 : took1 ? pos1 + 1 : pos1;
         }
         tc.expansions += both ? 2 : 1;
-        uint32_t nid = RB_EMPTY;
+        uint32_t nid = RB_EMPTY, npc = 0;
         {
             const bool upper_half = two && lane >= 16;
             const uint32_t col = two ? (uint32_t)(lane & 15) : (uint32_t)lane;
@@ -480,6 +486,7 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
                 uint32_t width;
                 const uint32_t* row = graph_row(g, key_slot(upper_half ? key2 : key1), level, width);
                 nid = __ldg(row + col);
+                npc = __ldg(graph_row_pc(g, row, level) + col);
             }
         }
         bool fresh = nid != RB_EMPTY && !bloom_test(w.bloom, nid, w.bloom_log2);
@@ -496,12 +503,13 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         if (!cnt)
             continue;
         if (fresh)
-            w.ids[__popc(mask & ((1u << lane) - 1u))] = nid;
+            w.ids[__popc(mask & ((1u << lane) - 1u))] = make_uint2(nid, npc);
         __syncwarp();
-        uint32_t id = (uint32_t)lane < cnt ? w.ids[lane] : 0u;
+        const uint2 staged = (uint32_t)lane < cnt ? w.ids[lane] : make_uint2(0u, 0u);
+        const uint32_t id = staged.x;
         __syncwarp();
         uint32_t cand;  // the candidate whose distance this lane received
-        uint32_t bits = warp_eval4(g.fp, qa, qb, id, cnt, cand);
+        uint32_t bits = warp_eval4(g.fp, qa, qb, id, staged.y, pq, cnt, cand);
         tc.distances += cnt;
         // qualify against the (possibly stale, hence only looser) worst list entry and park in pending
         const uint64_t key = make_key(bits, __shfl_sync(RB_FULL_MASK, id, cand & 31));
@@ -541,13 +549,21 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
         __syncwarp();
         return count;
     }
+    // Unions come from popcounts (|a| + |b| - intersection): |c| is counted once per candidate, |s| once per kept
+    // fingerprint (lane j keeps |kept_j| in `kept_pc`), so a (candidate, kept) pair costs only the AND-POPC half.
+    const uint32_t pq = group8_sum(popc4(q4));
+    uint32_t kept_pc = 0;
     // the closest candidate is always kept
     {
         uint64_t k0 = cand[0];
+        const uint4 a0 = load_slice(g.fp, key_slot(k0), sub);
         if (lane < 8)
-            w.kept[sub] = load_slice(g.fp, key_slot(k0), sub);
+            w.kept[sub] = a0;
         if (lane == 0)
             w.sel[0] = k0;
+        const uint32_t p0 = group8_sum(popc4(a0));
+        if (lane == 0)
+            kept_pc = p0;
     }
     __syncwarp();
     uint32_t kept = 1, c = 1;
@@ -557,12 +573,14 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
         uint64_t ck = have ? cand[ci] : 0ull;
         uint4 a = have ? load_slice(g.fp, key_slot(ck), sub) : make_uint4(0, 0, 0, 0);
         bool good = have;
-        const uint32_t vq = group8_inter_union(a, q4);
-        const uint32_t icq = vq & 0xFFFFu, ucq = (vq >> 16) ? (vq >> 16) : 1u;  // u == 0: ratio 0
+        const uint32_t vq = group8_sum(popc4_and(a, q4) | (popc4(a) << 16));
+        const uint32_t icq = vq & 0xFFFFu, pa = vq >> 16;
+        const uint32_t ucq = (pa + pq - icq) ? (pa + pq - icq) : 1u;  // u == 0: ratio 0
         for (uint32_t j = 0; j < kept; ++j) {
             uint4 s = w.kept[j * 8 + sub];
-            uint32_t v = group8_inter_union(a, s);
-            const uint32_t ics = v & 0xFFFFu, ucs = (v >> 16) ? (v >> 16) : 1u;
+            const uint32_t ics = group8_sum(popc4_and(a, s));
+            const uint32_t u = pa + __shfl_sync(RB_FULL_MASK, kept_pc, (int)j) - ics;
+            const uint32_t ucs = u ? u : 1u;
             good = good && !(ics * ucq > icq * ucs);  // counts <= 1024, unions <= 2048: no overflow
         }
         tc.distances += kept * (count - c < 4 ? count - c : 4);
@@ -576,6 +594,11 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
             w.kept[kept * 8 + sub] = a;
             if (sub == 0)
                 w.sel[kept] = ck;
+        }
+        {
+            const uint32_t pf = __shfl_sync(RB_FULL_MASK, pa, first * 8);
+            if ((uint32_t)lane == kept)
+                kept_pc = pf;
         }
         __syncwarp();
         ++kept;
@@ -631,8 +654,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_kernel(Inser
             uint32_t width;
             uint32_t* mine = graph_row(p.g, slot, level, width);
             uint64_t sk = (uint32_t)lane < ns ? w.sel[lane] : 0ull;
-            if ((uint32_t)lane < width)
+            const uint32_t spc = warp_popcounts(p.g.fp, key_slot(sk), ns);
+            if ((uint32_t)lane < width) {
                 mine[lane] = (uint32_t)lane < ns ? key_slot(sk) : RB_EMPTY;
+                graph_row_pc(p.g, mine, level)[lane] = (uint16_t)spc;
+            }
             if ((uint32_t)lane < p.g.m) {
                 size_t at = (size_t)task * p.g.m + lane;
                 bool on = (uint32_t)lane < ns;
@@ -743,8 +769,12 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(Rever
         return;
 
     if (deg + ni <= width) {
-        if ((uint32_t)lane < ni)
-            row[deg + lane] = (uint32_t)inc[lane];
+        const uint32_t src = (uint32_t)lane < ni ? (uint32_t)inc[lane] : 0u;
+        const uint32_t spc = warp_popcounts(p.g.fp, src, ni);
+        if ((uint32_t)lane < ni) {
+            row[deg + lane] = src;
+            graph_row_pc(p.g, row, level)[deg + lane] = (uint16_t)spc;
+        }
         return;
     }
 
@@ -787,10 +817,42 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(Rever
     cand[lane + 32] = b;
     __syncwarp();
     uint32_t ns = warp_select_neighbors(p.g, w, cand, nc, width, tc, t4);
-    if ((uint32_t)lane < width)
-        row[lane] = (uint32_t)lane < ns ? key_slot(w.sel[lane]) : RB_EMPTY;
+    {
+        const uint32_t nb = (uint32_t)lane < ns ? key_slot(w.sel[lane]) : RB_EMPTY;
+        const uint32_t spc = warp_popcounts(p.g.fp, nb, ns);
+        if ((uint32_t)lane < width) {
+            row[lane] = nb;
+            graph_row_pc(p.g, row, level)[lane] = (uint16_t)spc;
+        }
+    }
     if (lane == 0)
         atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+}
+
+// ------------------------------------------------------------------------------------------------ link popcounts
+// For a graph that arrives from a file (rb_load): popcount of every fingerprint (streaming, one 8-lane group per row),
+// then pc[link] = node_pc[adj[link]] for every link.  Graphs built here get their popcounts from the kernels above.
+__global__ void __launch_bounds__(256) node_popcount_kernel(const uint4* __restrict__ fp, uint32_t rows,
+                                                            uint16_t* __restrict__ out) {
+    const uint32_t sub = threadIdx.x & 7;
+    for (size_t row = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;; row += ((size_t)gridDim.x * blockDim.x) >> 3) {
+        // a warp leaves the loop as a whole, so that every lane takes part in the shuffles
+        const bool any = __any_sync(RB_FULL_MASK, row < rows);
+        if (!any)
+            break;
+        uint32_t v = group8_sum(row < rows ? popc4(__ldg(fp + row * 8 + sub)) : 0u);
+        if (row < rows && sub == 0)
+            out[row] = (uint16_t)v;
+    }
+}
+
+__global__ void __launch_bounds__(256) link_popcount_kernel(const uint32_t* __restrict__ adj, size_t links,
+                                                            const uint16_t* __restrict__ node_pc,
+                                                            uint16_t* __restrict__ out) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < links; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t id = __ldg(adj + i);
+        out[i] = id == RB_EMPTY ? (uint16_t)0 : __ldg(node_pc + id);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ approximate search

@@ -257,5 +257,7 @@ def test_full_size_build_properties():
     assert np.array_equal(res.distances.view(np.uint32), want.view(np.uint32))
     assert (res.distances[:, 0] == 0).mean() > 0.40
     exact = ix.search(q, k, exact=True)
-    assert (exact.distances[:, 0] == 0).all()
+    # every query is a row of the set and finds itself; query 0 is the all-zero row, whose distance to anything
+    # (itself included) is 1 by the reference's u == 0 rule (binary.h:104)
+    assert (exact.distances[1:, 0] == 0).all() and exact.distances[0, 0] == 1
     assert _recall(res.distances, exact.distances, k) > 0.40
