@@ -101,6 +101,8 @@ struct DeviceState {
     size_t work_counters_cap = 0;
     unsigned long long* counters = nullptr;  // [0] distances [1] expansions
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    cudaStream_t copy_stream = nullptr;  // metadata of the second segment of a large add (build_new_rows)
+    cudaEvent_t ev_copy = nullptr;
     int insert_blocks_per_sm = 0, search_blocks_per_sm = 0;
     int insert_variant = 4, search_variant = 4;
     uint32_t insert_cfg_ef = 0, search_cfg_ef = 0;
@@ -133,6 +135,10 @@ struct DeviceState {
             cudaEventDestroy(ev_begin);
         if (ev_end)
             cudaEventDestroy(ev_end);
+        if (ev_copy)
+            cudaEventDestroy(ev_copy);
+        if (copy_stream)
+            cudaStreamDestroy(copy_stream);
         if (stream)
             cudaStreamDestroy(stream);
         *this = DeviceState{};
@@ -315,6 +321,7 @@ struct Batch {
     uint32_t entry;
     int32_t max_level;
     uint32_t tasks;
+    uint32_t tasks_bound;  // size + sum of levels: known after pass 1, >= tasks
 };
 
 // run f(i) for i in [0, count) on up to 16 host threads (static interleaved split; f must be thread-safe per i)
@@ -338,20 +345,17 @@ void parallel_for(size_t count, size_t min_per_thread, F&& f) {
 }
 
 // The schedule is a pure function of (current size, levels): mirrored by tests/model/batched_model.c.
-void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all_levels /* old + new */,
-                  std::vector<Batch>& batches, std::vector<uint32_t>& task_rel /* per new node */,
-                  std::vector<uint32_t>& task_order /* per new node */, int32_t& max_level, uint64_t& entry) {
+// Pass 1 (sequential, cheap): batch boundaries, and the entry point / top level each batch starts from.
+void plan_batch_bounds(rb_index* ix, size_t old_size, std::vector<int16_t> const& all_levels /* old + new */,
+                       std::vector<Batch>& batches, int32_t& max_level, uint64_t& entry) {
     const size_t total = all_levels.size();
     const uint32_t den = ix->opts.batch_growth_den, bmax = ix->opts.batch_max;
     size_t s = old_size;
-    task_rel.assign(total - old_size, 0);
-    task_order.assign(total - old_size, 0);
-    // pass 1 (sequential, cheap): batch boundaries, and the entry point / top level each batch starts from
     while (s < total) {
         if (ix->opts.debug_max_batches && batches.size() >= ix->opts.debug_max_batches)
             break;
         if (s == 0) {
-            batches.push_back(Batch{0, 1, 0, -1, 0});  // the first node only becomes the entry point
+            batches.push_back(Batch{0, 1, 0, -1, 0, 0});  // the first node only becomes the entry point
             entry = 0;
             max_level = all_levels[0];
             s = 1;
@@ -362,6 +366,7 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
         b = std::min(b, total - s);
         bool raised = false;
         int32_t run_max = max_level;
+        uint32_t bound = 0;
         for (size_t t = 0; t < b; ++t) {
             if (all_levels[s + t] > run_max) {
                 if (raised) {
@@ -371,8 +376,9 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
                 raised = true;
                 run_max = all_levels[s + t];
             }
+            bound += 1u + (uint32_t)all_levels[s + t];
         }
-        batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, 0});
+        batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, 0, bound});
         if (raised)
             for (size_t t = 0; t < b; ++t)
                 if (all_levels[s + t] > max_level) {
@@ -381,11 +387,16 @@ void plan_batches(rb_index* ix, size_t old_size, std::vector<int16_t> const& all
                 }
         s += b;
     }
-    // pass 2 (one batch per task, on host threads): first task of every node, and the order of work inside the
-    // batch -- nodes with more levels to search first (longest job first), so the last wave of a launch holds only
-    // the short level-0 jobs; the nodes are independent, so any order gives the same graph.  Stable counting sort
-    // by the number of searched levels, descending.
-    parallel_for(batches.size(), 4, [&](size_t bi) {
+}
+
+// Pass 2 for batches [b0, b1) (one batch per task, on host threads): first task of every node, and the order of work
+// inside the batch -- nodes with more levels to search first (longest job first), so the last wave of a launch holds
+// only the short level-0 jobs; the nodes are independent, so any order gives the same graph.  Stable counting sort
+// by the number of searched levels, descending.  task_rel / task_order are indexed by new node.
+void plan_batch_tasks(size_t old_size, std::vector<int16_t> const& all_levels, std::vector<Batch>& batches, size_t b0,
+                      size_t b1, std::vector<uint32_t>& task_rel, std::vector<uint32_t>& task_order) {
+    parallel_for(b1 - b0, 4, [&](size_t rel) {
+        const size_t bi = b0 + rel;
         Batch& bt = batches[bi];
         if (bt.max_level < 0)
             return;
@@ -495,34 +506,60 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     std::vector<int16_t> all_levels(h.levels);
     all_levels.insert(all_levels.end(), new_levels.begin(), new_levels.end());
     std::vector<Batch> batches;
-    std::vector<uint32_t> task_rel, task_order;
+    std::vector<uint32_t> task_rel(n, 0), task_order(n, 0);
     int32_t max_level = h.max_level;
     uint64_t entry = h.entry;
     PhaseTimer pt;
-    plan_batches(ix, old_size, all_levels, batches, task_rel, task_order, max_level, entry);
-    pt.mark("  plan_batches");
+    plan_batch_bounds(ix, old_size, all_levels, batches, max_level, entry);
+    pt.mark("  plan_batch_bounds");
 
-    // per-node metadata of the new rows
+    // Per-node metadata of the new rows (upper-row offset, level, task tables) is prepared and uploaded in TWO
+    // segments: the batches over the first 1/16 of a large add are launched as soon as their own metadata is on the
+    // device, and the rest is prepared while the device works through them (uploaded on a second stream, so the copy
+    // does not queue behind those kernels).  The schedule and the graph do not depend on the split.
     std::vector<uint32_t> off32(n);
     std::vector<int8_t> lv8(n);
-    uint64_t upper = h.upper_off[old_size];
-    for (size_t i = 0; i < n; ++i) {
-        off32[i] = (uint32_t)upper;
-        upper += (uint64_t)new_levels[i];
+    uint64_t upper_run = h.upper_off[old_size];
+    size_t split_batch = batches.size(), split_row = n;  // batches [0, split_batch) = rows [0, split_row) go first
+    size_t segment_min_rows = (size_t)1 << 21;
+    if (char const* e = std::getenv("RB_SEGMENT_MIN_ROWS"))  // tests exercise the split on small adds
+        segment_min_rows = std::max<size_t>(16, std::strtoull(e, nullptr, 10));
+    if (n >= segment_min_rows)
+        for (size_t bi = 0; bi < batches.size(); ++bi)
+            if (batches[bi].start - old_size >= n / 16) {
+                split_batch = bi;
+                split_row = batches[bi].start - old_size;
+                break;
+            }
+    auto prepare_segment = [&](size_t b0, size_t b1, size_t r0, size_t r1, cudaStream_t stream) -> std::string {
+        if (r1 <= r0)
+            return {};
+        plan_batch_tasks(old_size, all_levels, batches, b0, b1, task_rel, task_order);
+        for (size_t i = r0; i < r1; ++i) {
+            off32[i] = (uint32_t)upper_run;
+            upper_run += (uint64_t)new_levels[i];
+        }
+        parallel_for((r1 - r0 + 65535) / 65536, 8, [&](size_t c) {
+            for (size_t i = r0 + c * 65536, e = std::min(r1, i + 65536); i < e; ++i)
+                lv8[i] = (int8_t)new_levels[i];
+        });
+        const size_t at = old_size + r0, cnt = r1 - r0;
+        RB_CUDA(cudaMemcpyAsync(d.upper_off + at, off32.data() + r0, cnt * 4, cudaMemcpyHostToDevice, stream));
+        RB_CUDA(cudaMemcpyAsync(d.levels + at, lv8.data() + r0, cnt, cudaMemcpyHostToDevice, stream));
+        RB_CUDA(cudaMemcpyAsync(d.task_rel + at, task_rel.data() + r0, cnt * 4, cudaMemcpyHostToDevice, stream));
+        RB_CUDA(cudaMemcpyAsync(d.task_order + at, task_order.data() + r0, cnt * 4, cudaMemcpyHostToDevice, stream));
+        return {};
+    };
+    {
+        std::string perr = prepare_segment(0, split_batch, 0, split_row, d.stream);
+        if (!perr.empty())
+            return perr;
     }
-    parallel_for((n + 65535) / 65536, 8, [&](size_t c) {
-        for (size_t i = c * 65536, e = std::min(n, i + 65536); i < e; ++i)
-            lv8[i] = (int8_t)new_levels[i];
-    });
-    RB_CUDA(cudaMemcpyAsync(d.upper_off + old_size, off32.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
-    RB_CUDA(cudaMemcpyAsync(d.levels + old_size, lv8.data(), n, cudaMemcpyHostToDevice, d.stream));
-    RB_CUDA(cudaMemcpyAsync(d.task_rel + old_size, task_rel.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
-    RB_CUDA(cudaMemcpyAsync(d.task_order + old_size, task_order.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
 
-    // scratch sized for the largest batch
+    // scratch sized for the largest batch (tasks_bound >= tasks is known for every batch after pass 1)
     size_t max_pairs = 0;
     for (Batch const& b : batches)
-        max_pairs = std::max(max_pairs, (size_t)b.tasks * h.m);
+        max_pairs = std::max(max_pairs, (size_t)b.tasks_bound * h.m);
     if (max_pairs > d.pair_cap) {
         size_t cap = ceil2(max_pairs);
         for (int i = 0; i < 2; ++i) {
@@ -569,9 +606,10 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         ticks.push_back(ev);
         return cudaEventRecord(ev, d.stream);
     };
-    pt.mark("  metadata uploads + scratch");
+    pt.mark("  first segment uploads + scratch");
     RB_CUDA(cudaEventRecord(d.ev_begin, d.stream));
-    for (size_t bi = 0; bi < batches.size(); ++bi) {
+    auto launch_batches = [&](size_t first_batch, size_t last_batch) -> std::string {
+    for (size_t bi = first_batch; bi < last_batch && !cancelled; ++bi) {
         Batch const& b = batches[bi];
         if (b.max_level >= 0) {
             rb::InsertParams ip;
@@ -635,6 +673,36 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
             }
         }
     }
+    return {};
+    };
+    {
+        std::string lerr = launch_batches(0, split_batch);
+        if (lerr.empty() && split_batch < batches.size() && !cancelled) {
+            // second segment: prepared while the device runs the first, uploaded beside it, then ordered after it
+            pt.mark("  first segment launched");
+            if (!d.copy_stream)
+                RB_CUDA(cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking));
+            if (!d.ev_copy)
+                RB_CUDA(cudaEventCreateWithFlags(&d.ev_copy, cudaEventDisableTiming));
+            lerr = prepare_segment(split_batch, batches.size(), split_row, n, d.copy_stream);
+            if (lerr.empty()) {
+                RB_CUDA(cudaEventRecord(d.ev_copy, d.copy_stream));
+                RB_CUDA(cudaStreamWaitEvent(d.stream, d.ev_copy, 0));
+                pt.mark("  second segment prepared");
+                lerr = launch_batches(split_batch, batches.size());
+            }
+        }
+        if (!lerr.empty()) {
+            cudaStreamSynchronize(d.stream);
+            if (d.copy_stream)
+                cudaStreamSynchronize(d.copy_stream);
+            for (cudaEvent_t ev : marks)
+                cudaEventDestroy(ev);
+            for (cudaEvent_t ev : ticks)
+                cudaEventDestroy(ev);
+            return lerr;
+        }
+    }
     RB_CUDA(cudaEventRecord(d.ev_end, d.stream));
     // Host bookkeeping of the new rows.  Without a progress callback nothing can cut the schedule short, so it runs
     // HERE, while the device is still working through the batches, and is undone if the device reports an error.
@@ -663,6 +731,13 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     pt.mark("  launch loop");
     if (early)
         commit(n);
+    // the host copy of the adjacency is read back right after the build unless the caller asked for a lazy sync:
+    // size (and page in) its destination now, while the device is busy, instead of inside the timed copy
+    const bool presize = early && !(ix->opts.flags & RB_FLAG_LAZY_HOST_SYNC);
+    if (presize) {
+        h.adj0.resize(h.keys.size() * (size_t)h.m0);
+        h.adju.resize(h.upper_off[h.keys.size()] * (size_t)h.m);
+    }
     pt.mark("  commit (device busy)");
     {
         cudaError_t e = cudaStreamSynchronize(d.stream);
@@ -671,6 +746,10 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         if (e != cudaSuccess) {
             if (early)
                 h.truncate_rows(old_size, old_max_level, old_entry);
+            if (presize) {
+                h.adj0.resize(old_size * (size_t)h.m0);
+                h.adju.resize(h.upper_off[old_size] * (size_t)h.m);
+            }
             for (cudaEvent_t ev : marks)
                 cudaEventDestroy(ev);
             for (cudaEvent_t ev : ticks)

@@ -108,13 +108,18 @@ __device__ __forceinline__ uint32_t warp_eval4_n(const uint4* __restrict__ fp, u
     static_assert(ROUNDS == 1 || ROUNDS == 2 || ROUNDS == 4, "rounds");
     const int lane = threadIdx.x & 31, sub = lane & 3, grp = lane >> 2;
     uint4 a[ROUNDS], b[ROUNDS];
+    // A group without a candidate (j >= cnt) re-reads the last candidate's line -- the same line another group of this
+    // very instruction requests, so it costs no traffic -- instead of zero-filling eight registers under a predicate;
+    // its result is discarded below (cand >= cnt).  Rounds without any candidate are skipped (warp-uniform).
+    const uint32_t jmax = cnt - 1;  // cnt >= 1
 #pragma unroll
     for (int r = 0; r < ROUNDS; ++r) {
-        uint32_t j = r * 8 + grp;
-        uint32_t id = __shfl_sync(RB_FULL_MASK, ids, j & 31);
-        const bool on = j < cnt;
-        a[r] = on ? load_slice(fp, id, sub) : make_uint4(0, 0, 0, 0);
-        b[r] = on ? load_slice(fp, id, sub + 4) : make_uint4(0, 0, 0, 0);
+        if (r == 0 || (uint32_t)(r * 8) < cnt) {
+            uint32_t j = r * 8 + grp;
+            uint32_t id = __shfl_sync(RB_FULL_MASK, ids, (j < jmax ? j : jmax) & 31);
+            a[r] = load_slice(fp, id, sub);
+            b[r] = load_slice(fp, id, sub + 4);
+        }
     }
     uint32_t v[ROUNDS];
 #pragma unroll

@@ -277,7 +277,7 @@ class Index:
             if not isinstance(keys, Iterable):
                 assert count == 1, "Each vector must have a key"
                 keys = [keys]
-            keys = np.array(keys).astype(Key)
+            keys = np.asarray(keys, dtype=Key)  # no copy when the caller already holds uint64 keys
         assert len(keys) == count
         if vectors.dtype != np.uint8:
             raise ValueError("Incompatible scalars in the vectors matrix: rad_b200 stores packed bits (numpy uint8)")

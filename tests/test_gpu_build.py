@@ -51,6 +51,22 @@ def test_graph_is_bit_exact_with_the_batched_model(n, m, ef_add):
     assert c["visited_members"] == mc["expansions"]
 
 
+def test_two_segment_metadata_upload_does_not_change_the_graph(monkeypatch):
+    """Adds of >= 2 M rows launch the batches over their first 1/16 while the metadata of the rest is still being
+    prepared (api.cu: build_new_rows); forced here on a small add: same graph as the model, bit for bit."""
+    n, m, ef_add = 9000, 8, 64
+    db = synth.clustered_fingerprints(n, seed=5)
+    monkeypatch.setenv("RB_SEGMENT_MIN_ROWS", "1000")
+    ix = _build(db, m, ef_add)
+    monkeypatch.delenv("RB_SEGMENT_MIN_ROWS")
+    lv, _ = O.levels(n, m)
+    model = M.BatchedModel(db, lv, connectivity=m, expansion_add=ef_add)
+    model.build()
+    adj0, adju = ix._debug_adjacency()
+    assert np.array_equal(adj0, model.adj0()) and np.array_equal(adju, model.adju())
+    assert np.array_equal(ix.levels, lv) and ix.entry_slot == model.entry
+
+
 def test_incremental_adds_equal_one_add():
     """Index.add called three times == called once (the level stream and the batch schedule continue)."""
     n = 5000
