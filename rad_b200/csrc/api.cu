@@ -578,12 +578,14 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         }
         d.pair_cap = cap;
     }
-    if (batches.size() > d.work_counters_cap) {
+    // two work counters per batch: insert_kernel's (nodes) at [bi], reverse_link_kernel's (pairs) at [batches + bi]
+    if (2 * batches.size() > d.work_counters_cap) {
         cudaFree(d.work_counters);
-        d.work_counters_cap = ceil2(batches.size());
+        d.work_counters_cap = ceil2(2 * batches.size());
         RB_CUDA(cudaMalloc(&d.work_counters, d.work_counters_cap * sizeof(unsigned int)));
     }
-    RB_CUDA(cudaMemsetAsync(d.work_counters, 0, std::max<size_t>(batches.size(), 1) * sizeof(unsigned int), d.stream));
+    RB_CUDA(cudaMemsetAsync(d.work_counters, 0, std::max<size_t>(2 * batches.size(), 1) * sizeof(unsigned int),
+                            d.stream));
     RB_CUDA(cudaMemsetAsync(d.counters, 0, 4 * sizeof(unsigned long long), d.stream));
 
     std::string err = configure_traversal_kernels(ix);
@@ -645,7 +647,10 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
             rp.pair_vals = d.pair_vals[1];
             rp.pair_count = (uint32_t)pairs;
             rp.counters = d.counters;
-            unsigned rblocks = (unsigned)((pairs + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock);
+            rp.work_counter = d.work_counters + batches.size() + bi;
+            // persistent warps taking 32 pairs at a time: no more CTAs than fit the SMs at once
+            unsigned rblocks = (unsigned)std::min<size_t>((pairs + 32 * rb::kWarpsPerBlock - 1) / (32 * rb::kWarpsPerBlock),
+                                                          (size_t)d.sm_count * 8);
             if (time_kernels)
                 RB_CUDA(tick());
             rb::reverse_link_kernel<<<rblocks, rb::kWarpsPerBlock * 32, 0, d.stream>>>(rp);

@@ -689,6 +689,7 @@ struct ReverseParams {
     const uint64_t* pair_vals;
     uint32_t pair_count;
     unsigned long long* counters;
+    unsigned int* work_counter;  // zeroed before the launch: warps take 32 pairs at a time
 };
 
 // bitonic sort of 64 keys held two per lane (a: index lane, b: index lane + 32), ascending
@@ -718,27 +719,11 @@ __device__ __forceinline__ void warp_sort64(uint64_t& a, uint64_t& b) {
     }
 }
 
-__global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(ReverseParams p) {
-    __shared__ __align__(16) unsigned char smem[kWarpsPerBlock * (kMaxWidth * 128 + kMaxWidth * 8 + kCandMax * 8 +
-                                                                   kIncomingCap * 8)];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
-    unsigned char* base = smem + (size_t)warp * (kMaxWidth * 128 + kMaxWidth * 8 + kCandMax * 8 + kIncomingCap * 8);
-    WarpScratch w;
-    w.kept = reinterpret_cast<uint4*>(base);
-    w.sel = reinterpret_cast<uint64_t*>(base + kMaxWidth * 128);
-    uint64_t* cand = reinterpret_cast<uint64_t*>(base + kMaxWidth * 128 + kMaxWidth * 8);
-    uint64_t* inc = cand + kCandMax;
-    w.list = nullptr;
-    w.bloom = nullptr;
-    w.ids = nullptr;
-    w.bloom_log2 = 0;
-
-    const uint32_t i = blockIdx.x * kWarpsPerBlock + warp;
-    if (i >= p.pair_count)
-        return;
+// one (level, target) segment of the sorted pair list, starting at pair i (its head), by one warp
+__device__ __forceinline__ void reverse_link_segment(const ReverseParams& p, const WarpScratch& w, uint64_t* cand,
+                                                     uint64_t* inc, uint32_t i) {
+    const int lane = threadIdx.x & 31, sub = lane & 7;
     const uint64_t key = p.pair_keys[i];
-    if (key == ~0ull || (i > 0 && p.pair_keys[i - 1] == key))
-        return;  // not the head of a (level, target) segment
     const int level = (int)(key >> 32);
     const uint32_t target = (uint32_t)key;
     TraversalCounters tc{0, 0};
@@ -832,6 +817,43 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(Rever
     }
     if (lane == 0)
         atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+}
+
+// Persistent warps: a warp takes 32 consecutive pairs at a time, finds the segment heads among them with one
+// coalesced read, and works through those segments.  (One warp per PAIR left most warps of a CTA idle from their
+// first instruction -- only heads have work -- while the CTA kept its slots until its busiest warp finished.)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) reverse_link_kernel(ReverseParams p) {
+    __shared__ __align__(16) unsigned char smem[kWarpsPerBlock * (kMaxWidth * 128 + kMaxWidth * 8 + kCandMax * 8 +
+                                                                   kIncomingCap * 8)];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* base = smem + (size_t)warp * (kMaxWidth * 128 + kMaxWidth * 8 + kCandMax * 8 + kIncomingCap * 8);
+    WarpScratch w;
+    w.kept = reinterpret_cast<uint4*>(base);
+    w.sel = reinterpret_cast<uint64_t*>(base + kMaxWidth * 128);
+    uint64_t* cand = reinterpret_cast<uint64_t*>(base + kMaxWidth * 128 + kMaxWidth * 8);
+    uint64_t* inc = cand + kCandMax;
+    w.list = nullptr;
+    w.bloom = nullptr;
+    w.ids = nullptr;
+    w.bloom_log2 = 0;
+    for (;;) {
+        uint32_t first = 0;
+        if (lane == 0)
+            first = atomicAdd(p.work_counter, 32u);
+        first = __shfl_sync(RB_FULL_MASK, first, 0);
+        if (first >= p.pair_count)
+            break;
+        const uint32_t i = first + lane;
+        bool head = false;
+        if (i < p.pair_count) {
+            const uint64_t key = p.pair_keys[i];
+            head = key != ~0ull && (i == 0 || p.pair_keys[i - 1] != key);
+        }
+        for (uint32_t heads = __ballot_sync(RB_FULL_MASK, head); heads; heads &= heads - 1) {
+            reverse_link_segment(p, w, cand, inc, first + (uint32_t)__ffs((int)heads) - 1);
+            __syncwarp();
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------------ link popcounts
