@@ -23,8 +23,13 @@ namespace rb {
 
 constexpr int kTQ = 128;             // queries per CTA (UMMA M)
 constexpr int kTD = 256;             // database rows per tile (UMMA N)
-constexpr int kTChunkBytes = 128;    // unpacked K bytes per stage (= 128 fingerprint bits = one uint4 per row)
-constexpr int kTStages = 2;
+#ifndef RB_I8_PIECES
+#define RB_I8_PIECES 8
+#endif
+constexpr int kTPieces = RB_I8_PIECES;         // 16-byte K pieces (= 16 fingerprint bits each) per B stage: 8 or 4
+constexpr int kTStages = 16 / kTPieces;        // the B ring is 64 KB: 2 stages of 128 bits or 4 stages of 64 bits
+                                               // (measured: 4 x 64 bits is 20 % slower -- two MMAs per commit)
+constexpr int kTSteps = 64 / kTPieces;         // B stages per database tile
 constexpr int kTEpiWarps = 4, kTMmaWarp = 4, kTProdWarp0 = 5, kTProdWarps = 8;
 constexpr int kTThreads = (kTEpiWarps + 1 + kTProdWarps) * 32;  // 416
 constexpr int kTQueueCap = kTQ * 8;   // survivors of one 8-column round of a block, worst case (32 queries x 8 per warp)
@@ -35,7 +40,7 @@ constexpr int kTListK = 16;           // top-k lists of up to this k live in sha
 //   address(row, k16) = (row / 8) * SBO + k16 * LBO + (row % 8) * 16
 constexpr uint32_t kLBO = 128;
 constexpr uint32_t kSBO_A = 64 * kLBO;  // A holds all 64 K pieces of a row group
-constexpr uint32_t kSBO_B = 8 * kLBO;   // a B stage holds 8
+constexpr uint32_t kSBO_B = kTPieces * kLBO;   // a B stage holds kTPieces
 constexpr uint32_t kASmemBytes = (kTQ / 8) * kSBO_A;          // 131072
 constexpr uint32_t kBStageBytes = (kTD / 8) * kSBO_B;         // 32768
 
@@ -99,14 +104,27 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 // N >> 3 at [17,23), M >> 4 at [24,29)
 constexpr uint32_t kIdescI8 = (2u << 4) | ((uint32_t)(kTD >> 3) << 17) | ((uint32_t)(kTQ >> 4) << 24);
 
-// 32 fingerprint bits -> 32 bytes of 0/1 as two 16-byte K pieces.  Any fixed bit -> K position mapping works as long
-// as both operands use it, so the cheapest one is taken: output word j holds bits j, j+8, j+16, j+24 of the input
-// word, i.e. (w >> j) & 0x01010101 -- one shift and one AND per four bits.
-__device__ __forceinline__ uint4 unpack_half(uint32_t w, int half) {
+// 32 fingerprint bits -> 32 bytes as two 16-byte K pieces.  Any fixed bit -> K position mapping works as long as both
+// operands use it, so the cheapest one is taken: output word j holds bits j, j+8, j+16, j+24 of the input word.
+// The DATABASE side, unpacked for every tile, leaves each bit where it is inside its byte: w & (0x01010101 << j), ONE
+// instruction per four bits, byte value 2^j.  The QUERY side, unpacked once per CTA, compensates with byte value
+// 2^(7-j): every matching bit contributes 2^j * 2^(7-j) = 128, so the accumulators hold 128 x intersection
+// (<= 2^17, exact in s32) and the epilogue's thresholds are scaled by 128 instead of the counts being shifted.
+constexpr int kTScaleLog2 = 7;
+__device__ __forceinline__ uint4 unpack_half_db(uint32_t w, int half) {
     const uint32_t m = 0x01010101u;
     const int j = half * 4;
-    return make_uint4((w >> j) & m, (w >> (j + 1)) & m, (w >> (j + 2)) & m, (w >> (j + 3)) & m);
+    return make_uint4(w & (m << j), w & (m << (j + 1)), w & (m << (j + 2)), w & (m << (j + 3)));
 }
+__device__ __forceinline__ uint4 unpack_half_query(uint32_t w, int half) {
+    const uint32_t m = 0x01010101u;
+    const int j = half * 4;
+    return make_uint4(((w >> j) & m) << (7 - j), ((w >> (j + 1)) & m) << (6 - j), ((w >> (j + 2)) & m) << (5 - j),
+                      ((w >> (j + 3)) & m) << (4 - j));
+}
+// padding rows carry this "popcount": >= 2048 keeps them out while a list is not full (see the filter), and small
+// enough that 128 * y * |d| stays inside 32 bits
+constexpr uint32_t kTPadRow = 4096;
 
 #define RB_TICK(slot, expr)                                      \
     do {                                                         \
@@ -171,7 +189,8 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
             int r = idx & (kTQ - 1), k16 = idx >> 7;
             uint32_t q = q0 + r;
             uint32_t w = q < p.query_count ? __ldg(q32 + (size_t)q * 32 + (k16 >> 1)) : 0u;
-            *reinterpret_cast<uint4*>(smem_a + (r >> 3) * kSBO_A + k16 * kLBO + (r & 7) * 16) = unpack_half(w, k16 & 1);
+            *reinterpret_cast<uint4*>(smem_a + (r >> 3) * kSBO_A + k16 * kLBO + (r & 7) * 16) =
+                unpack_half_query(w, k16 & 1);
         }
     }
     if (tid == 0) {
@@ -221,22 +240,25 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 pc += popc4(v[c]);
-                const uint64_t g = t * 8 + c;
-                const int st = (int)(g & (kTStages - 1));
-                RB_TICK(1, mbar_wait(&s.empty[st], (uint32_t)(((g / kTStages) & 1) ^ 1)));
-                unsigned char* dst = my_b + st * kBStageBytes;
                 const uint32_t w[4] = {v[c].x, v[c].y, v[c].z, v[c].w};
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    *reinterpret_cast<uint4*>(dst + j * kLBO) = unpack_half(w[j >> 1], j & 1);
-                fence_proxy_async();
-                __syncwarp();
-                if (lane == 0)
-                    mbar_arrive(&s.full[st]);
+                for (int h = 0; h < 8 / kTPieces; ++h) {  // K piece c * 8 + h * kTPieces + j  <->  A piece of the same index
+                    const uint64_t g = t * kTSteps + c * (8 / kTPieces) + h;
+                    const int st = (int)(g & (kTStages - 1));
+                    RB_TICK(1, mbar_wait(&s.empty[st], (uint32_t)(((g / kTStages) & 1) ^ 1)));
+                    unsigned char* dst = my_b + st * kBStageBytes;
+#pragma unroll
+                    for (int j = 0; j < kTPieces; ++j)
+                        *reinterpret_cast<uint4*>(dst + j * kLBO) = unpack_half_db(w[(h * kTPieces + j) >> 1], j & 1);
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(&s.full[st]);
+                }
             }
             const int a = (int)(t & 1);
             RB_TICK(2, mbar_wait(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));  // epilogue of tile t-2 done with pd[a]
-            s.pd[a][pr] = row < row_end ? pc : kXInvalid;
+            s.pd[a][pr] = row < row_end ? pc : kTPadRow;
             __syncwarp();
             if (lane == 0)
                 mbar_arrive(&s.pd_full[a]);
@@ -249,21 +271,21 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
             const int a = (int)(t & 1);
             RB_TICK(1, mbar_wait(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
             tc_fence_after();
-            for (int c = 0; c < 8; ++c) {
-                const uint64_t g = t * 8 + c;
+            for (int c = 0; c < kTSteps; ++c) {
+                const uint64_t g = t * kTSteps + c;
                 const int st = (int)(g & (kTStages - 1));
                 RB_TICK(2, mbar_wait(&s.full[st], (uint32_t)((g / kTStages) & 1)));
                 tc_fence_after();
                 if (lane == 0) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
+                    for (int j = 0; j < kTPieces / 2; ++j) {
                         // K = 32 bytes per instruction = two 16-byte K pieces
-                        uint64_t ad = a_desc0 + (uint64_t)(((c * 8 + j * 2) * kLBO) >> 4);
+                        uint64_t ad = a_desc0 + (uint64_t)(((c * kTPieces + j * 2) * kLBO) >> 4);
                         uint64_t bd = b_desc0 + (uint64_t)((st * kBStageBytes + j * 2 * kLBO) >> 4);
                         tc_mma_i8(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8, (uint32_t)((c | j) != 0));
                     }
                     tc_commit(&s.empty[st]);
-                    if (c == 7)
+                    if (c == kTSteps - 1)
                         tc_commit(&s.tmem_full[a]);
                 }
                 __syncwarp();
@@ -299,11 +321,11 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
                 //     i * A + w > B + y * |d|      (A = u_t + i_t, y = i_t, B = i_t |q|, w = 0; see exact_kernels.cuh)
                 // i.e. iff  dlt = (y |d| + B - w) - i A  is negative; its sign bit is funnel-shifted into one of four
                 // independent 8-bit masks (pair 8 r + j of the block ends up at bit 7 - j of mask r).  Padding rows
-                // (|d| = 0xFFFF, i = 0) never pass.
+                // (|d| = kTPadRow, i = 0) never pass.  The accumulators hold 128 i: y, B and w are scaled to match.
                 uint32_t hm[4] = {0, 0, 0, 0};
                 {
                     const uint4 th = s.thr[ql];
-                    const uint32_t neg_a = 0u - th.x, bw = th.z - th.w, y = th.y;
+                    const uint32_t neg_a = 0u - th.x, bw = (th.z - th.w) << kTScaleLog2, y = th.y << kTScaleLog2;
                     const uint4* pd4 = reinterpret_cast<const uint4*>(&s.pd[a][b * 32]);
 #pragma unroll
                     for (int g = 0; g < 8; ++g) {
@@ -335,7 +357,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
                             uint32_t iv = 0;
 #pragma unroll
                             for (int e = 0; e < 8; ++e)  // acc[] lives in registers: select without dynamic indexing
-                                iv = (e == j) ? acc[r * 8 + e] : iv;
+                                iv = (e == j) ? (acc[r * 8 + e] >> kTScaleLog2) : iv;
                             uint32_t at = atomicAdd(&s.queue_count[warp], 1u);
                             s.queue[warp][at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + r * 8 + j) << 16) | iv;
                         }
