@@ -876,19 +876,23 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
 // ================================================================================================ search
 namespace {
 
+#ifndef RB_I8_PAIR_DEFAULT
+#define RB_I8_PAIR_DEFAULT 0  // 1: CTA pairs (cta_group::2) whenever the tensor-core kernel runs on more than one tile
+#endif
 struct ExactPlan {
     bool tensor;  // tcgen05 int8 kernel (128-query tiles, 256-row stages) instead of the POPC kernel (64 x 64)
+    bool pair;    // ... in its CTA-pair form (exact_topk_i8_kernel_t<true>)
     uint32_t chunks;
     uint64_t chunk_rows;
     size_t keys_bytes, iu_bytes;
 };
 
-// RB_EXACT_KERNEL=popc|i8 forces one of the two bit-identical kernels (tests, profiling)
+// RB_EXACT_KERNEL=popc|i8|i8x2 forces one of the bit-identical kernels (tests, profiling)
 int exact_kernel_override() {
     char const* e = std::getenv("RB_EXACT_KERNEL");  // read per call: tests flip it between calls
     if (!e)
         return 0;
-    return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : 0;
+    return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : std::strcmp(e, "i8x2") == 0 ? 3 : 0;
 }
 
 ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
@@ -897,16 +901,36 @@ ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     // the tensor-core tile is 128 queries wide: worth it once at least half a tile is used and there are enough
     // pairs per CTA to amortise unpacking the queries and warming up the per-CTA top-k lists (measured crossover
     // with the POPC kernel: about 1e9 pairs)
-    p.tensor = forced == 2 || (forced == 0 && nq >= 64 && rows * nq >= 2000000000ull);
+    p.tensor = forced >= 2 || (forced == 0 && nq >= 64 && rows * nq >= 2000000000ull);
+    // CTA pairs (cta_group::2): two adjacent query tiles share every unpacked database tile
+    p.pair = forced == 3 || (forced == 0 && p.tensor && RB_I8_PAIR_DEFAULT && nq > (uint64_t)rb::kTQ);
     const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.tensor ? rb::kTD : rb::kXD;
     const uint64_t resident = p.tensor ? 148 : 296;  // CTAs resident on the 148 SMs
     uint64_t qtiles = std::max<uint64_t>(1, (nq + tq - 1) / tq);
+    if (p.pair)
+        qtiles = (qtiles + 1) & ~(uint64_t)1;
     uint64_t row_tiles = std::max<uint64_t>(1, (rows + td - 1) / td);
-    uint64_t want = std::max<uint64_t>(1, (4 * resident + qtiles - 1) / qtiles);  // about 4 waves
-    uint64_t chunks = std::min(want, row_tiles);
-    uint64_t tiles_per_chunk = (row_tiles + chunks - 1) / chunks;
+    // Database chunks: 3 to 8 waves of CTAs, and among those the count that leaves the LAST wave fullest -- all CTAs of a
+    // launch run equally long, so 632 CTAs on 148 SMs (4.27 waves) cost five full waves (measured: 15 % of the launch)
+    uint64_t best_chunks = 1, best_tpc = row_tiles;
+    double best_util = -1.0;
+    const uint64_t c_lo = std::max<uint64_t>(1, (3 * resident + qtiles - 1) / qtiles);
+    const uint64_t c_hi = std::max<uint64_t>(c_lo, (8 * resident) / qtiles);
+    for (uint64_t c = c_lo; c <= c_hi; ++c) {
+        const uint64_t cc = std::min(c, row_tiles);
+        const uint64_t tpc = (row_tiles + cc - 1) / cc;
+        const uint64_t real = (row_tiles + tpc - 1) / tpc;  // chunks after rounding to whole tiles
+        const uint64_t ctas = real * qtiles, waves = (ctas + resident - 1) / resident;
+        const double util = (double)ctas / (double)(waves * resident);
+        if (util > best_util + 1e-9) {
+            best_util = util;
+            best_chunks = real;
+            best_tpc = tpc;
+        }
+    }
+    const uint64_t tiles_per_chunk = best_tpc;
     p.chunk_rows = tiles_per_chunk * td;
-    p.chunks = (uint32_t)((row_tiles + tiles_per_chunk - 1) / tiles_per_chunk);
+    p.chunks = (uint32_t)best_chunks;
     p.keys_bytes = ((size_t)p.chunks * nq * k * 8 + 255) & ~(size_t)255;
     p.iu_bytes = ((size_t)p.chunks * nq * k * 4 + 255) & ~(size_t)255;
     return p;
@@ -928,7 +952,9 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     if (!configured) {
         RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(rb::ExactSmem)));
-        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)rb::kTensorSmemBytes));
+        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)rb::kTensorSmemBytes));
         configured = true;
     }
@@ -951,9 +977,25 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
         RB_CUDA(cudaMemsetAsync(dbg_dev, 0, 32 * sizeof(unsigned long long), stream));
         ep.debug_cycles = dbg_dev;
     }
-    if (pl.tensor) {
+    if (pl.tensor && pl.pair) {
+        unsigned qt = (unsigned)((nq + rb::kTQ - 1) / rb::kTQ);
+        qt = (qt + 1u) & ~1u;  // whole pairs: the odd CTA of the last pair has no valid query but unpacks its half
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(qt, pl.chunks);
+        cfg.blockDim = dim3(rb::kTThreads);
+        cfg.dynamicSmemBytes = rb::kTensorSmemBytes;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        RB_CUDA(cudaLaunchKernelEx(&cfg, rb::exact_topk_i8_kernel_t<true>, ep));
+    } else if (pl.tensor) {
         dim3 grid((unsigned)((nq + rb::kTQ - 1) / rb::kTQ), pl.chunks);  // query tiles fastest: CTAs resident
-        rb::exact_topk_i8_kernel<<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
+        rb::exact_topk_i8_kernel_t<false><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
     } else {
         dim3 grid(pl.chunks, (unsigned)((nq + rb::kXQ - 1) / rb::kXQ));
         rb::exact_topk_kernel<<<grid, rb::kXThreads, sizeof(rb::ExactSmem), stream>>>(ep);

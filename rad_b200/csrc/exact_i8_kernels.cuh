@@ -53,9 +53,10 @@ struct TensorSmemTail {
     unsigned long long lkeys[kTQ][kTListK];  // per-query sorted partial lists (k <= kTListK), written back at the end
     uint32_t liu[kTQ][kTListK];
     uint32_t tmem_base;
-    unsigned long long full[kTStages], empty[kTStages], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
+    unsigned long long full[4], empty[4], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
 };
 constexpr size_t kTensorSmemBytes = kASmemBytes + kTStages * kBStageBytes + sizeof(TensorSmemTail) + 1024;
+static_assert(kTStages <= 4, "barrier arrays");
 
 // ---------------------------------------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -76,6 +77,52 @@ __device__ __forceinline__ void mbar_wait(void* bar, uint32_t parity) {
             : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)
             : "memory");
     } while (!done);
+}
+// ---- cluster (CTA pair) variants: barriers and popcounts of the peer CTA are reached through shared::cluster addresses
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(const void* local, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(local)), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, uint32_t v) {
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(void* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.b32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(void* bar) {  // arrives on the barrier at this offset in BOTH CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((unsigned short)3)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_mma_i8_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -103,6 +150,7 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 // instruction descriptor (InstrDescriptor): c_format = S32 (2) at [4,6), a/b format = UINT8 (0), both K-major,
 // N >> 3 at [17,23), M >> 4 at [24,29)
 constexpr uint32_t kIdescI8 = (2u << 4) | ((uint32_t)(kTD >> 3) << 17) | ((uint32_t)(kTQ >> 4) << 24);
+constexpr uint32_t kIdescI8Pair = (2u << 4) | ((uint32_t)(kTD >> 3) << 17) | ((uint32_t)((2 * kTQ) >> 4) << 24);
 
 // 32 fingerprint bits -> 32 bytes as two 16-byte K pieces.  Any fixed bit -> K position mapping works as long as both
 // operands use it, so the cheapest one is taken: output word j holds bits j, j+8, j+16, j+24 of the input word.
@@ -148,7 +196,24 @@ constexpr uint32_t kTPadRow = 4096;
         : "memory")
 
 // grid = (query tiles of 128, database chunks); ExactParams as for exact_topk_kernel with chunk_rows a multiple of kTD
-__global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams p) {
+//
+// PAIR = true: the kernel is launched in clusters of two CTAs along x (two adjacent query tiles, the same database
+// chunk) and the MMAs are `cta_group::2` (M = 256: each CTA's own 128 queries; N = 256: each CTA unpacks and stores
+// HALF of every database tile, 128 rows, and the tensor cores of both SMs read both halves).  Per unit of MMA work a
+// CTA then unpacks half as many rows and its shared-memory port serves 8 KB instead of 12 KB per MMA; the 64 KB B
+// ring holds 4 stages of 128 fingerprint bits instead of 2.  Only the leader CTA (rank 0) issues MMAs; `full` and
+// `tmem_empty` live in the leader and collect arrivals from both CTAs, `tcgen05.commit` multicasts `empty` and
+// `tmem_full` to both, and the row popcounts are written into both CTAs' side arrays through shared::cluster stores.
+template <bool PAIR>
+__global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactParams p) {
+    constexpr int STAGES = PAIR ? 4 : kTStages;             // B ring stages
+    constexpr int PIECES = PAIR ? 8 : kTPieces;             // K pieces per stage
+    constexpr int STEPS = 64 / PIECES;                      // stages per database tile
+    constexpr int BROWS = PAIR ? kTD / 2 : kTD;             // database rows this CTA unpacks per tile
+    constexpr uint32_t SBO_B = PIECES * kLBO;
+    constexpr uint32_t STAGE_BYTES = (BROWS / 8) * SBO_B;
+    static_assert(STAGES * STAGE_BYTES == kTStages * kBStageBytes, "the B ring is 64 KB in either variant");
+    const uint32_t rank = PAIR ? cluster_rank() : 0u;
     // no swizzle: the operand descriptors only need 16-byte alignment, which dynamic shared memory guarantees; the
     // array is used directly so that every access stays in the shared address space (LDS / STS, not generic LD / ST)
     extern __shared__ __align__(1024) unsigned char raw[];
@@ -156,7 +221,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
     unsigned char* smem_b = raw + kASmemBytes;
     TensorSmemTail& s = *reinterpret_cast<TensorSmemTail*>(raw + kASmemBytes + kTStages * kBStageBytes);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t q0 = blockIdx.x * kTQ;
+    const uint32_t q0 = blockIdx.x * kTQ;  // may lie past the last query (the odd CTA of the last pair): all rows invalid
     const uint32_t chunk = blockIdx.y;
     const uint64_t row_begin = (uint64_t)chunk * p.chunk_rows;
     const uint64_t row_end = row_begin + p.chunk_rows < p.rows ? row_begin + p.chunk_rows : p.rows;
@@ -164,7 +229,8 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
 
     // ---- the CTA's partial lists start empty
     {
-        uint32_t nq = p.query_count - q0 < (uint32_t)kTQ ? p.query_count - q0 : (uint32_t)kTQ;
+        uint32_t nq = q0 >= p.query_count ? 0u
+                      : p.query_count - q0 < (uint32_t)kTQ ? p.query_count - q0 : (uint32_t)kTQ;
         size_t base = ((size_t)chunk * p.query_count + q0) * p.k;
         for (size_t i = tid; i < (size_t)nq * p.k; i += kTThreads)
             p.partial_keys[base + i] = ~0ull;
@@ -194,28 +260,38 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
         }
     }
     if (tid == 0) {
-        for (int i = 0; i < kTStages; ++i) {
-            mbar_init(&s.full[i], kTProdWarps);  // one arrival per producer WARP (256 arrivals on one word serialise)
+        constexpr uint32_t ctas = PAIR ? 2 : 1;
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(&s.full[i], ctas * kTProdWarps);  // one arrival per producer WARP (256 arrivals on one word serialise)
             mbar_init(&s.empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s.tmem_full[i], 1);
-            mbar_init(&s.tmem_empty[i], kTEpiWarps);
-            mbar_init(&s.pd_full[i], kTProdWarps);
-            mbar_init(&s.pd_empty[i], kTEpiWarps);
+            mbar_init(&s.tmem_empty[i], ctas * kTEpiWarps);
+            mbar_init(&s.pd_full[i], ctas * kTProdWarps);
+            mbar_init(&s.pd_empty[i], ctas * kTEpiWarps);
         }
         for (int i = 0; i < kTEpiWarps; ++i)
             s.queue_count[i] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kTMmaWarp) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&s.tmem_base))
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&s.tmem_base))
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&s.tmem_base))
+                         : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     fence_proxy_async();  // the A operand was written through the generic proxy
     tc_fence_before();
-    __syncthreads();
+    if (PAIR)
+        cluster_sync_all();  // both CTAs' barriers are initialised and both A operands are in place
+    else
+        __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = s.tmem_base;
     const bool dbg = p.debug_cycles != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
@@ -225,6 +301,53 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
     if (warp >= kTProdWarp0) {
         // ================================================================ producers: one database row per thread
         const int pr = tid - kTProdWarp0 * 32;  // 0 .. 255
+        if constexpr (PAIR) {
+            // two threads per row (row = pr / 2 of this CTA's 128; half = which 64 bits of every 128-bit K chunk), so
+            // that all 256 producer threads work on every stage
+            const int prow = pr >> 1, half = pr & 1;
+            unsigned char* my_b = smem_b + (prow >> 3) * SBO_B + (prow & 7) * 16 + half * 4 * kLBO;
+            const uint32_t full_leader = map_to_cta(&s.full[0], 0);
+            for (uint64_t t = 0; t < n_tiles; ++t) {
+                const uint64_t tile = n_tiles - 1 - t;  // highest rows first (see exact_kernels.cuh)
+                const uint64_t row = row_begin + tile * kTD + rank * BROWS + prow;
+                uint2 v[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    v[c] = row < row_end ? __ldg(reinterpret_cast<const uint2*>(p.db + row * 8 + c) + half)
+                                         : make_uint2(0, 0);
+                uint32_t pc = 0;
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    pc += __popc(v[c].x) + __popc(v[c].y);
+                    const uint64_t g = t * STEPS + c;
+                    const int st = (int)(g & (STAGES - 1));
+                    mbar_wait_cluster(&s.empty[st], (uint32_t)(((g / STAGES) & 1) ^ 1));
+                    unsigned char* dst = my_b + st * STAGE_BYTES;
+                    const uint32_t w[2] = {v[c].x, v[c].y};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)  // K piece c * 8 + half * 4 + j  <->  A piece of the same index
+                        *reinterpret_cast<uint4*>(dst + j * kLBO) = unpack_half_db(w[j >> 1], j & 1);
+                    fence_proxy_async();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive_cluster(full_leader + (uint32_t)st * 8u);
+                }
+                pc += __shfl_xor_sync(RB_FULL_MASK, pc, 1);
+                const int a = (int)(t & 1);
+                mbar_wait_cluster(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));  // both epilogues done with pd[a]
+                if (half == 0) {
+                    const uint32_t val = row < row_end ? pc : kTPadRow;
+                    st_cluster_u32(map_to_cta(&s.pd[a][rank * BROWS + prow], 0), val);
+                    st_cluster_u32(map_to_cta(&s.pd[a][rank * BROWS + prow], 1), val);
+                }
+                asm volatile("fence.acq_rel.cluster;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) {
+                    mbar_arrive_cluster(map_to_cta(&s.pd_full[a], 0));
+                    mbar_arrive_cluster(map_to_cta(&s.pd_full[a], 1));
+                }
+            }
+        } else {
         unsigned char* my_b = smem_b + (pr >> 3) * kSBO_B + (pr & 7) * 16;
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;  // highest rows first (see exact_kernels.cuh)
@@ -263,30 +386,46 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
             if (lane == 0)
                 mbar_arrive(&s.pd_full[a]);
         }
+        }
     } else if (warp == kTMmaWarp) {
         // ================================================================ MMA issuer
         const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), kLBO, kSBO_A);
-        const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), kLBO, kSBO_B);
-        for (uint64_t t = 0; t < n_tiles; ++t) {
+        const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), kLBO, SBO_B);
+        for (uint64_t t = 0; t < n_tiles && rank == 0; ++t) {  // in a pair only the leader CTA issues
             const int a = (int)(t & 1);
-            RB_TICK(1, mbar_wait(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
+            if (PAIR)
+                mbar_wait_cluster(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
+            else
+                RB_TICK(1, mbar_wait(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
             tc_fence_after();
-            for (int c = 0; c < kTSteps; ++c) {
-                const uint64_t g = t * kTSteps + c;
-                const int st = (int)(g & (kTStages - 1));
-                RB_TICK(2, mbar_wait(&s.full[st], (uint32_t)((g / kTStages) & 1)));
+            for (int c = 0; c < STEPS; ++c) {
+                const uint64_t g = t * STEPS + c;
+                const int st = (int)(g & (STAGES - 1));
+                if (PAIR)
+                    mbar_wait_cluster(&s.full[st], (uint32_t)((g / STAGES) & 1));
+                else
+                    RB_TICK(2, mbar_wait(&s.full[st], (uint32_t)((g / STAGES) & 1)));
                 tc_fence_after();
                 if (lane == 0) {
 #pragma unroll
-                    for (int j = 0; j < kTPieces / 2; ++j) {
+                    for (int j = 0; j < PIECES / 2; ++j) {
                         // K = 32 bytes per instruction = two 16-byte K pieces
-                        uint64_t ad = a_desc0 + (uint64_t)(((c * kTPieces + j * 2) * kLBO) >> 4);
-                        uint64_t bd = b_desc0 + (uint64_t)((st * kBStageBytes + j * 2 * kLBO) >> 4);
-                        tc_mma_i8(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8, (uint32_t)((c | j) != 0));
+                        uint64_t ad = a_desc0 + (uint64_t)(((c * PIECES + j * 2) * kLBO) >> 4);
+                        uint64_t bd = b_desc0 + (uint64_t)((st * STAGE_BYTES + j * 2 * kLBO) >> 4);
+                        if (PAIR)
+                            tc_mma_i8_pair(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8Pair, (uint32_t)((c | j) != 0));
+                        else
+                            tc_mma_i8(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8, (uint32_t)((c | j) != 0));
                     }
-                    tc_commit(&s.empty[st]);
-                    if (c == kTSteps - 1)
-                        tc_commit(&s.tmem_full[a]);
+                    if (PAIR) {
+                        tc_commit_pair(&s.empty[st]);
+                        if (c == STEPS - 1)
+                            tc_commit_pair(&s.tmem_full[a]);
+                    } else {
+                        tc_commit(&s.empty[st]);
+                        if (c == STEPS - 1)
+                            tc_commit(&s.tmem_full[a]);
+                    }
                 }
                 __syncwarp();
             }
@@ -299,11 +438,18 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;
             const int a = (int)(t & 1);
-            RB_TICK(0, mbar_wait(&s.pd_full[a], (uint32_t)((t >> 1) & 1)));
-            RB_TICK(1, mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1)));
+            if (PAIR) {
+                mbar_wait_cluster(&s.pd_full[a], (uint32_t)((t >> 1) & 1));
+                mbar_wait_cluster(&s.tmem_full[a], (uint32_t)((t >> 1) & 1));
+            } else {
+                RB_TICK(0, mbar_wait(&s.pd_full[a], (uint32_t)((t >> 1) & 1)));
+                RB_TICK(1, mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1)));
+            }
             tc_fence_after();
             // 32-column blocks from the HIGHEST rows down: the thresholds move between blocks, and a row that only ties
             // the k-th distance must never displace a higher slot (same invariant as the tile order)
+            // (Keeping the TMEM read of block b-1 in flight while block b is filtered -- two register buffers -- was
+            // measured 5 % SLOWER: 128 registers with spills, and the read competes with the MMAs' accumulator traffic.)
             for (int b = kTD / 32 - 1; b >= 0; --b) {
                 uint32_t acc[32];
                 const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * kTD + b * 32);
@@ -314,8 +460,12 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
                 if (b == 0) {  // the accumulator stage is free as soon as the last block is in registers
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive(&s.tmem_empty[a]);
+                    if (lane == 0) {
+                        if (PAIR)
+                            mbar_arrive_cluster(map_to_cta(&s.tmem_empty[a], 0));
+                        else
+                            mbar_arrive(&s.tmem_empty[a]);
+                    }
                 }
                 // exact integer filter, 3 instructions per pair: the pair passes iff
                 //     i * A + w > B + y * |d|      (A = u_t + i_t, y = i_t, B = i_t |q|, w = 0; see exact_kernels.cuh)
@@ -406,8 +556,14 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
                     dbg_acc[7] += qn_total;
                 }
             }
-            if (lane == 0)
-                mbar_arrive(&s.pd_empty[a]);
+            if (lane == 0) {
+                if (PAIR) {
+                    mbar_arrive_cluster(map_to_cta(&s.pd_empty[a], 0));
+                    mbar_arrive_cluster(map_to_cta(&s.pd_empty[a], 1));
+                } else {
+                    mbar_arrive(&s.pd_empty[a]);
+                }
+            }
         }
         if (smem_lists && pqv != kXInvalid) {  // publish this query's partial list
             size_t off = ((size_t)chunk * p.query_count + q0 + ql) * p.k;
@@ -422,9 +578,17 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams
             p.debug_cycles[role * 10 + 1 + i] = dbg_acc[i];
         p.debug_cycles[31] = n_tiles;
     }
-    __syncthreads();
-    if (warp == kTMmaWarp)
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+    tc_fence_before();
+    if (PAIR)
+        cluster_sync_all();  // no CTA may leave (or free its TMEM) while its peer still reads its shared memory
+    else
+        __syncthreads();
+    if (warp == kTMmaWarp) {
+        if (PAIR)
+            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+        else
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+    }
 }
 
 }  // namespace rb

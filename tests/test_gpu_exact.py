@@ -14,10 +14,11 @@ from rad_b200.index import Index
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["popc", "i8"])
+@pytest.fixture(autouse=True, params=["popc", "i8", "i8x2"])
 def exact_kernel(request, monkeypatch):
-    """Every test of this module runs against BOTH exact-search kernels: the POPC-pipe kernel and the tcgen05 int8
-    tensor-core kernel (rad_b200/csrc/exact_i8_kernels.cuh); the library reads RB_EXACT_KERNEL on every call."""
+    """Every test of this module runs against ALL exact-search kernels: the POPC-pipe kernel, the tcgen05 int8
+    tensor-core kernel and its CTA-pair (cta_group::2) form (rad_b200/csrc/exact_i8_kernels.cuh); the library reads
+    RB_EXACT_KERNEL on every call."""
     monkeypatch.setenv("RB_EXACT_KERNEL", request.param)
     return request.param
 
