@@ -884,7 +884,8 @@ struct ExactPlan {
     bool pair;    // ... in its CTA-pair form (exact_topk_i8_kernel_t<true>)
     uint32_t chunks;
     uint64_t chunk_rows;
-    size_t keys_bytes, iu_bytes;
+    size_t keys_bytes, iu_bytes;  // iu_bytes includes the per-query bound words at bounds_off
+    size_t bounds_off;            // u64[Q] shared k-th-distance bounds (tensor-core kernels), from the workspace start
 };
 
 // RB_EXACT_KERNEL=popc|i8|i8x2 forces one of the bit-identical kernels (tests, profiling)
@@ -928,11 +929,18 @@ ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
             best_tpc = tpc;
         }
     }
+    if (char const* e = std::getenv("RB_EXACT_CHUNKS")) {  // profiling aid: force the chunk count
+        const uint64_t cc = std::min<uint64_t>(std::max<uint64_t>(1, std::strtoull(e, nullptr, 10)), row_tiles);
+        best_tpc = (row_tiles + cc - 1) / cc;
+        best_chunks = (row_tiles + best_tpc - 1) / best_tpc;
+    }
     const uint64_t tiles_per_chunk = best_tpc;
     p.chunk_rows = tiles_per_chunk * td;
     p.chunks = (uint32_t)best_chunks;
     p.keys_bytes = ((size_t)p.chunks * nq * k * 8 + 255) & ~(size_t)255;
     p.iu_bytes = ((size_t)p.chunks * nq * k * 4 + 255) & ~(size_t)255;
+    p.bounds_off = p.keys_bytes + p.iu_bytes;
+    p.iu_bytes += ((size_t)nq * 8 + 255) & ~(size_t)255;
     return p;
 }
 
@@ -969,6 +977,11 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     ep.chunk_rows = pl.chunk_rows;
     ep.partial_keys = static_cast<uint64_t*>(workspace);
     ep.partial_iu = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(workspace) + pl.keys_bytes);
+    ep.bounds = reinterpret_cast<unsigned long long*>(static_cast<uint8_t*>(workspace) + pl.bounds_off);
+    if (pl.tensor && pl.chunks <= 512)  // the bound word has 9 bits for the chunk
+        RB_CUDA(cudaMemsetAsync(ep.bounds, 0xFF, (size_t)nq * 8, stream));
+    else
+        ep.bounds = nullptr;
     ep.debug_cycles = nullptr;
     static unsigned long long* dbg_dev = nullptr;
     if (pl.tensor && std::getenv("RB_EXACT_DEBUG")) {

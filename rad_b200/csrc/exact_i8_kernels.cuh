@@ -435,6 +435,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         const int ql = warp * 32 + lane;
         const uint32_t pqv = s.pq[ql];
         const bool smem_lists = p.k <= (uint32_t)kTListK;
+        const bool share_bounds = smem_lists && p.bounds != nullptr;  // bound word: d bits << 32 | chunk << 23 | i << 12 | u
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;
             const int a = (int)(t & 1);
@@ -446,6 +447,23 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                 RB_TICK(1, mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1)));
             }
             tc_fence_after();
+            // Shared bounds.  Every CTA starts with empty lists, and until a list is full and tight nearly every pair
+            // survives the filter (about k ln(rows/k) survivors per query and CTA, ~1.5 k cycles each on the slow path:
+            // 2.9 ms per CTA at k = 10).  The k-th best distance ANY CTA has reached for a query bounds the final k-th
+            // distance from above, so it is published (atomicMin below) and adopted here whenever it is tighter than
+            // this CTA's own.  The bound word carries the CHUNK it was found in: chunks are ascending slot ranges, so a
+            // row of a lower chunk that merely ties the bound loses to the k rows behind it (strict test, w = 0), while
+            // a row of a higher chunk wins the tie on its slot (non-strict, w = 1).  Which survivors take the slow path
+            // depends on timing; the result does not.
+            if (share_bounds && pqv != kXInvalid) {
+                const unsigned long long g = __ldcg(p.bounds + q0 + ql);
+                const unsigned long long own = s.lkeys[ql][p.k - 1];
+                if (g != ~0ull && (own == ~0ull || (uint32_t)(g >> 32) < (uint32_t)(own >> 32))) {
+                    const uint32_t holder = (uint32_t)(g >> 23) & 0x1FFu;
+                    const uint32_t it_ = (uint32_t)(g >> 12) & 0x7FFu, ut = (uint32_t)g & 0xFFFu;
+                    s.thr[ql] = make_uint4(ut + it_, it_, it_ * pqv, chunk < holder ? 0u : 1u);
+                }
+            }
             // 32-column blocks from the HIGHEST rows down: the thresholds move between blocks, and a row that only ties
             // the k-th distance must never displace a higher slot (same invariant as the tile order)
             // (Keeping the TMEM read of block b-1 in flight while block b is filtered -- two register buffers -- was
@@ -519,6 +537,8 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                             for (uint32_t jj = 0; jj < 32 && base + jj < qn; ++jj) {
                                 uint32_t ev = __shfl_sync(RB_FULL_MASK, e, (int)jj);
                                 uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
+                                if (s.pd[a][dl] >= kTPadRow)  // a padding row can pass a non-strict bound with i_t = 0
+                                    continue;                 // (warp-uniform: every lane looks at the same entry)
                                 uint32_t u = s.pq[eq] + s.pd[a][dl] - i;
                                 uint32_t slot = (uint32_t)(p.slot_base + row_begin + tile * kTD + dl);
                                 uint64_t key = ((uint64_t)exact_distance_bits(i, u) << 32) | (uint32_t)~slot;
@@ -536,8 +556,13 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                                 if (lk[p.k - 1] != ~0ull) {
                                     uint32_t iu = li[p.k - 1];
                                     uint32_t it_ = iu & 0xFFFFu, ut = iu >> 16;
-                                    if (lane == 0)
+                                    if (lane == 0) {
                                         s.thr[eq] = make_uint4(ut + it_, it_, it_ * s.pq[eq], 0);
+                                        if (share_bounds)
+                                            atomicMin(p.bounds + q0 + eq,
+                                                      ((lk[p.k - 1] >> 32) << 32) | ((unsigned long long)chunk << 23) |
+                                                          ((unsigned long long)it_ << 12) | ut);
+                                    }
                                 }
                                 __syncwarp();
                             }

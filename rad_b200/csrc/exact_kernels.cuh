@@ -36,6 +36,8 @@ struct ExactParams {
     uint64_t chunk_rows;    // multiple of kXD
     uint64_t* partial_keys; // [chunks x Q x k]  distance bits << 32 | ~slot ; ~0 = empty
     uint32_t* partial_iu;   // [chunks x Q x k]  i | u << 16 of each entry
+    unsigned long long* bounds;        // [Q], ~0 at launch (tensor-core kernels): the smallest k-th-best key any CTA has
+                                       // reached for the query so far, distance bits << 32 | i << 16 | u
     unsigned long long* debug_cycles;  // optional [32] cycle counters of the tensor kernel's roles (profiling aid)
 };
 
