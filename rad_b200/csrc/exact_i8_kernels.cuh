@@ -349,17 +349,27 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
             }
         } else {
         unsigned char* my_b = smem_b + (pr >> 3) * kSBO_B + (pr & 7) * 16;
+        // the row of tile t + 1 is requested while tile t is unpacked (its L2 latency is off the hand-off path), and the
+        // pieces of a stage are formed in registers BEFORE the wait for the stage, so that only stores follow the wait
+        uint4 v[8];
+        {
+            const uint64_t row0 = row_begin + (n_tiles - 1) * kTD + pr;
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                v[c] = row0 < row_end ? __ldg(p.db + row0 * 8 + c) : make_uint4(0, 0, 0, 0);
+        }
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;  // highest rows first (see exact_kernels.cuh)
             const uint64_t row = row_begin + tile * kTD + pr;
-            uint4 v[8];
-            long long tl0 = dbg ? clock64() : 0;
+            uint4 vn[8];
+            {
+                const uint64_t rown = row - kTD;  // tile - 1 (only used when t + 1 < n_tiles; always < row_end then)
+                const bool more = t + 1 < n_tiles;
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
-                v[c] = row < row_end ? __ldg(p.db + row * 8 + c) : make_uint4(0, 0, 0, 0);
+                for (int c = 0; c < 8; ++c)
+                    vn[c] = more ? __ldg(p.db + rown * 8 + c) : make_uint4(0, 0, 0, 0);
+            }
             uint32_t pc = 0;
-            if (dbg)
-                dbg_acc[0] += (unsigned long long)(clock64() - tl0) + (v[0].x & 0);
 #pragma unroll
             for (int c = 0; c < 8; ++c) {
                 pc += popc4(v[c]);
@@ -368,17 +378,24 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                 for (int h = 0; h < 8 / kTPieces; ++h) {  // K piece c * 8 + h * kTPieces + j  <->  A piece of the same index
                     const uint64_t g = t * kTSteps + c * (8 / kTPieces) + h;
                     const int st = (int)(g & (kTStages - 1));
+                    uint4 u[kTPieces];
+#pragma unroll
+                    for (int j = 0; j < kTPieces; ++j)
+                        u[j] = unpack_half_db(w[(h * kTPieces + j) >> 1], j & 1);
                     RB_TICK(1, mbar_wait(&s.empty[st], (uint32_t)(((g / kTStages) & 1) ^ 1)));
                     unsigned char* dst = my_b + st * kBStageBytes;
 #pragma unroll
                     for (int j = 0; j < kTPieces; ++j)
-                        *reinterpret_cast<uint4*>(dst + j * kLBO) = unpack_half_db(w[(h * kTPieces + j) >> 1], j & 1);
+                        *reinterpret_cast<uint4*>(dst + j * kLBO) = u[j];
                     fence_proxy_async();
                     __syncwarp();
                     if (lane == 0)
                         mbar_arrive(&s.full[st]);
                 }
             }
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                v[c] = vn[c];
             const int a = (int)(t & 1);
             RB_TICK(2, mbar_wait(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));  // epilogue of tile t-2 done with pd[a]
             s.pd[a][pr] = row < row_end ? pc : kTPadRow;
