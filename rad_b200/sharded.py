@@ -107,3 +107,71 @@ class ShardedExactSearch:
                                        torch.cuda.current_stream().cuda_stream, C.byref(err))
         self._native.check(err)
         return merged
+
+
+class ShardedIndex:
+    """The reference's multi-index search (``Indexes``: usearch/python/usearch/index.py:1389-1482, lib.cpp:417-498,
+    merge rule index.hpp:2625-2645) for one process per GPU: every rank holds a sub-index over a contiguous shard of
+    the rows; ``search`` runs on every shard (exact or ef-bounded, on that rank's GPU), all-gathers the per-shard
+    ``[Q, k]`` answers and merges them, so every rank returns the same ``BatchMatches``.
+
+    ``local_index`` is a ``rad_b200.index.Index`` (or anything with its ``add`` / ``search`` signature) whose slots are
+    this shard's rows in order; ``slot_base`` is the global slot of its first row.  Results carry the user's keys;
+    ordering is the reference's: ascending distance, ties by descending GLOBAL slot.  The exchange is
+    ``2 x Q x k x 8`` bytes per rank through ``torch.distributed`` (NCCL on GPUs, gloo in the CPU tests)."""
+
+    def __init__(self, local_index, slot_base: int):
+        import torch
+        self._torch = torch
+        self.local = local_index
+        self.slot_base = int(slot_base)
+        dist = torch.distributed
+        self._dist = dist if dist.is_available() and dist.is_initialized() else None
+        self.world = self._dist.get_world_size() if self._dist else 1
+
+    def __len__(self) -> int:
+        n = len(self.local)
+        if self._dist is None:
+            return n
+        t = self._tensor(np.array([n], dtype=np.int64))
+        self._dist.all_reduce(t)
+        return int(t.cpu().item())
+
+    def add(self, keys, vectors, **kw):
+        """Insert this rank's rows (``keys`` are the user's keys of those rows) into the local sub-index."""
+        return self.local.add(keys, vectors, **kw)
+
+    def _tensor(self, a: np.ndarray):
+        t = self._torch.from_numpy(np.ascontiguousarray(a))
+        if self._dist is not None and self._dist.get_backend() == "nccl":
+            t = t.cuda()
+        return t
+
+    def search(self, vectors, count: int = 10, *, exact: bool = False):
+        from .index import BatchMatches
+        vectors = np.atleast_2d(vectors)
+        got = self.local.search(vectors, count, exact=exact)
+        nq = len(vectors)
+        keys = np.asarray(got.keys, dtype=np.uint64).reshape(nq, count)
+        dists = np.asarray(got.distances, dtype=np.float32).reshape(nq, count)
+        counts = np.asarray(got.counts, dtype=np.int64).reshape(nq)
+        # merge key = distance bits << 32 | ~global slot; the local slot of a result is recovered from its key
+        slots = np.asarray(self.local.get_node_ids_from_keys(keys.reshape(-1)), dtype=np.uint64).reshape(nq, count)
+        mkeys = pack_topk_keys(dists, slots + np.uint64(self.slot_base), counts)
+        if self._dist is None:
+            return got
+        both = np.stack([mkeys.view(np.int64), keys.view(np.int64)])            # [2, Q, k]
+        part = self._tensor(both)
+        gathered = self._torch.empty((self.world,) + tuple(part.shape), dtype=part.dtype, device=part.device)
+        self._dist.all_gather_into_tensor(gathered.view(-1), part.contiguous().view(-1))
+        g = gathered.cpu().numpy()                                               # [world, 2, Q, k]
+        flat_m = np.transpose(g[:, 0], (1, 0, 2)).reshape(nq, self.world * count).view(np.uint64)
+        flat_k = np.transpose(g[:, 1], (1, 0, 2)).reshape(nq, self.world * count).view(np.uint64)
+        order = np.argsort(flat_m, axis=1, kind="stable")[:, :count]
+        merged = np.take_along_axis(flat_m, order, axis=1)
+        out_keys = np.take_along_axis(flat_k, order, axis=1)
+        _, out_d, out_c = unpack_topk_keys(merged)
+        out_keys = np.where(merged != EMPTY_KEY, out_keys, 0)
+        return BatchMatches(keys=out_keys, distances=out_d, counts=out_c,
+                            visited_members=int(getattr(got, "visited_members", 0)),
+                            computed_distances=int(getattr(got, "computed_distances", 0)))

@@ -72,3 +72,59 @@ def test_two_rank_gather_and_merge_equals_unsharded(tmp_path, n, nq, k):
     b = np.load(tmp_path / "merged_1.npy")
     assert np.array_equal(a, b)      # every rank holds the same merged answer
     assert np.array_equal(a, want)   # and it is the unsharded reference answer, ties included
+
+
+class _OracleShard:
+    """Stands in for rad_b200.index.Index on a rank without a GPU: same search / key-lookup surface, answers from the
+    oracle over this rank's rows; user keys are global row + 1000 (not the slots)."""
+
+    def __init__(self, rows, lo):
+        self.rows, self.lo = rows, lo
+
+    def __len__(self):
+        return len(self.rows)
+
+    def search(self, vectors, count=10, *, exact=False):
+        from rad_b200.index import BatchMatches
+        slots, dists, counts = O.exact_search(self.rows, vectors, count)
+        keys = slots.astype(np.uint64) + np.uint64(self.lo + 1000)
+        return BatchMatches(keys=keys, distances=dists, counts=counts)
+
+    def get_node_ids_from_keys(self, keys):
+        return np.asarray(keys, dtype=np.int64) - (self.lo + 1000)
+
+
+def _sharded_index_worker(rank, world, port, n, nq, k, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        db = synth.clustered_fingerprints(n, seed=23)
+        q = synth.heldout_queries(nq, seed=23, n_total=n)
+        lo, hi = sharded.shard_bounds(n, world, rank)
+        ix = sharded.ShardedIndex(_OracleShard(db[lo:hi], lo), lo)
+        assert len(ix) == n
+        got = ix.search(q, k, exact=True)
+        np.savez(os.path.join(out_dir, f"sharded_{rank}.npz"), keys=got.keys, distances=got.distances,
+                 counts=got.counts)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,nq,k", [(1501, 21, 10), (7, 3, 10)])
+def test_sharded_index_search_equals_unsharded(tmp_path, n, nq, k):
+    """ShardedIndex.search over two ranks == one search over all rows: user keys, float bits, counts, tie order."""
+    world = 2
+    mp.spawn(_sharded_index_worker, args=(world, _free_port(), n, nq, k, str(tmp_path)), nprocs=world, join=True)
+    db = synth.clustered_fingerprints(n, seed=23)
+    q = synth.heldout_queries(nq, seed=23, n_total=n)
+    slots, dists, counts = O.exact_search(db, q, k)
+    a = np.load(tmp_path / "sharded_0.npz")
+    b = np.load(tmp_path / "sharded_1.npz")
+    for name in ("keys", "distances", "counts"):
+        assert np.array_equal(a[name], b[name])
+    assert np.array_equal(a["counts"], counts)
+    for r in range(nq):
+        c = int(counts[r])
+        assert np.array_equal(a["keys"][r, :c], slots[r, :c].astype(np.uint64) + np.uint64(1000))
+        assert np.array_equal(a["distances"][r, :c].view(np.uint32), dists[r, :c].view(np.uint32))
