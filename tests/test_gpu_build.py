@@ -67,6 +67,27 @@ def test_two_segment_metadata_upload_does_not_change_the_graph(monkeypatch):
     assert np.array_equal(ix.levels, lv) and ix.entry_slot == model.entry
 
 
+def test_add_after_load_continues_the_same_build(tmp_path):
+    """add(a); add(b) == add(a); save; load; add(b), bit for bit: the loader restores the level stream, uploads the
+    graph and rebuilds the device-only link popcounts (node_popcount_kernel + link_popcount_kernel) that the traversal
+    of the second add reads."""
+    n1, n2 = 3000, 2500
+    db = synth.clustered_fingerprints(n1 + n2, seed=41)
+    keys = np.arange(n1 + n2, dtype=np.uint64)
+    a = Index(ndim=1024, connectivity=8, expansion_add=64)
+    a.add(keys[:n1], db[:n1])
+    path = str(tmp_path / "first.usearch")
+    a.save(path)
+    a.add(keys[n1:], db[n1:])
+    b = Index(ndim=1024, connectivity=8, expansion_add=64)
+    b.load(path)
+    b.add(keys[n1:], db[n1:])
+    assert np.array_equal(a.levels, b.levels) and a.entry_slot == b.entry_slot and a.max_level == b.max_level
+    a0, au = a._debug_adjacency()
+    b0, bu = b._debug_adjacency()
+    assert np.array_equal(a0, b0) and np.array_equal(au, bu)
+
+
 def test_incremental_adds_equal_one_add():
     """Index.add called three times == called once (the level stream and the batch schedule continue)."""
     n = 5000
