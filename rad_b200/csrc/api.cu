@@ -876,24 +876,29 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
 // ================================================================================================ search
 namespace {
 
+#ifndef RB_I8_TS_DEFAULT
+#define RB_I8_TS_DEFAULT 0  // 1: the tensor-core kernel keeps the query operand in tensor memory (MODE 2)
+#endif
 #ifndef RB_I8_PAIR_DEFAULT
 #define RB_I8_PAIR_DEFAULT 0  // 1: CTA pairs (cta_group::2) whenever the tensor-core kernel runs on more than one tile
 #endif
 struct ExactPlan {
     bool tensor;  // tcgen05 int8 kernel (128-query tiles, 256-row stages) instead of the POPC kernel (64 x 64)
-    bool pair;    // ... in its CTA-pair form (exact_topk_i8_kernel_t<true>)
+    bool pair;    // ... in its CTA-pair form (exact_topk_i8_kernel_t<1>)
+    bool ts;      // ... with the query operand in tensor memory (exact_topk_i8_kernel_t<2>)
     uint32_t chunks;
     uint64_t chunk_rows;
     size_t keys_bytes, iu_bytes;  // iu_bytes includes the per-query bound words at bounds_off
     size_t bounds_off;            // u64[Q] shared k-th-distance bounds (tensor-core kernels), from the workspace start
 };
 
-// RB_EXACT_KERNEL=popc|i8|i8x2 forces one of the bit-identical kernels (tests, profiling)
+// RB_EXACT_KERNEL=popc|i8|i8x2|i8ts forces one of the bit-identical kernels (tests, profiling)
 int exact_kernel_override() {
     char const* e = std::getenv("RB_EXACT_KERNEL");  // read per call: tests flip it between calls
     if (!e)
         return 0;
-    return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : std::strcmp(e, "i8x2") == 0 ? 3 : 0;
+    return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : std::strcmp(e, "i8x2") == 0 ? 3
+           : std::strcmp(e, "i8ts") == 0 ? 4 : 0;
 }
 
 ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
@@ -905,6 +910,7 @@ ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     p.tensor = forced >= 2 || (forced == 0 && nq >= 64 && rows * nq >= 2000000000ull);
     // CTA pairs (cta_group::2): two adjacent query tiles share every unpacked database tile
     p.pair = forced == 3 || (forced == 0 && p.tensor && RB_I8_PAIR_DEFAULT && nq > (uint64_t)rb::kTQ);
+    p.ts = forced == 4 || (forced == 0 && p.tensor && !p.pair && RB_I8_TS_DEFAULT);
     const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.tensor ? rb::kTD : rb::kXD;
     const uint64_t resident = p.tensor ? 148 : 296;  // CTAs resident on the 148 SMs
     uint64_t qtiles = std::max<uint64_t>(1, (nq + tq - 1) / tq);
@@ -960,9 +966,11 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     if (!configured) {
         RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)sizeof(rb::ExactSmem)));
-        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)rb::kTensorSmemBytes));
-        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)rb::kTensorSmemBytes));
+        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)rb::kTensorSmemBytes));
         configured = true;
     }
@@ -1005,10 +1013,13 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
-        RB_CUDA(cudaLaunchKernelEx(&cfg, rb::exact_topk_i8_kernel_t<true>, ep));
+        RB_CUDA(cudaLaunchKernelEx(&cfg, rb::exact_topk_i8_kernel_t<1>, ep));
     } else if (pl.tensor) {
         dim3 grid((unsigned)((nq + rb::kTQ - 1) / rb::kTQ), pl.chunks);  // query tiles fastest: CTAs resident
-        rb::exact_topk_i8_kernel_t<false><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
+        if (pl.ts)
+            rb::exact_topk_i8_kernel_t<2><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);
+        else
+            rb::exact_topk_i8_kernel_t<0><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
     } else {
         dim3 grid(pl.chunks, (unsigned)((nq + rb::kXQ - 1) / rb::kXQ));
         rb::exact_topk_kernel<<<grid, rb::kXThreads, sizeof(rb::ExactSmem), stream>>>(ep);

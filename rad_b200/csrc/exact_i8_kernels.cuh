@@ -53,10 +53,11 @@ struct TensorSmemTail {
     unsigned long long lkeys[kTQ][kTListK];  // per-query sorted partial lists (k <= kTListK), written back at the end
     uint32_t liu[kTQ][kTListK];
     uint32_t tmem_base;
-    unsigned long long full[4], empty[4], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
+    unsigned long long full[8], empty[8], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
 };
 constexpr size_t kTensorSmemBytes = kASmemBytes + kTStages * kBStageBytes + sizeof(TensorSmemTail) + 1024;
-static_assert(kTStages <= 4, "barrier arrays");
+static_assert(kTStages <= 8, "barrier arrays");
+static_assert(kTensorSmemBytes <= 232448, "227 KB of shared memory per CTA");
 
 // ---------------------------------------------------------------------------------------------- PTX helpers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -114,6 +115,16 @@ __device__ __forceinline__ void tc_commit_pair(void* bar) {  // arrives on the b
     asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                  ::"r"(smem_u32(bar)), "h"((unsigned short)3)
                  : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void tc_mma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                             uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 __device__ __forceinline__ void tc_mma_i8_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                                uint32_t accumulate) {
@@ -204,21 +215,29 @@ constexpr uint32_t kTPadRow = 4096;
 // ring holds 4 stages of 128 fingerprint bits instead of 2.  Only the leader CTA (rank 0) issues MMAs; `full` and
 // `tmem_empty` live in the leader and collect arrivals from both CTAs, `tcgen05.commit` multicasts `empty` and
 // `tmem_full` to both, and the row popcounts are written into both CTAs' side arrays through shared::cluster stores.
-template <bool PAIR>
+//
+// MODE 2 (TS): the query operand lives in TENSOR MEMORY (tcgen05.mma with A from TMEM: 137 instead of 166 cycles per
+// M128 N256 K32 instruction, and no operand bytes of A through the shared-memory port).  TMEM then holds A (columns
+// 256..511) and ONE 256-column accumulator, so the MMAs of a tile wait for the epilogue of the previous one; the
+// 128 KB of shared memory that A leaves make the B ring 6 stages deep.
+template <int MODE>
 __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactParams p) {
-    constexpr int STAGES = PAIR ? 4 : kTStages;             // B ring stages
+    constexpr bool PAIR = MODE == 1, TS = MODE == 2;
+    constexpr int STAGES = PAIR ? 4 : TS ? 6 : kTStages;    // B ring stages
     constexpr int PIECES = PAIR ? 8 : kTPieces;             // K pieces per stage
     constexpr int STEPS = 64 / PIECES;                      // stages per database tile
     constexpr int BROWS = PAIR ? kTD / 2 : kTD;             // database rows this CTA unpacks per tile
     constexpr uint32_t SBO_B = PIECES * kLBO;
     constexpr uint32_t STAGE_BYTES = (BROWS / 8) * SBO_B;
-    static_assert(STAGES * STAGE_BYTES == kTStages * kBStageBytes, "the B ring is 64 KB in either variant");
+    static_assert(TS ? STAGES * STAGE_BYTES == kASmemBytes + kTStages * kBStageBytes
+                     : STAGES * STAGE_BYTES == kTStages * kBStageBytes,
+                  "the B ring is 64 KB behind the query operand, or all 192 KB without it");
     const uint32_t rank = PAIR ? cluster_rank() : 0u;
     // no swizzle: the operand descriptors only need 16-byte alignment, which dynamic shared memory guarantees; the
     // array is used directly so that every access stays in the shared address space (LDS / STS, not generic LD / ST)
     extern __shared__ __align__(1024) unsigned char raw[];
     unsigned char* smem_a = raw;
-    unsigned char* smem_b = raw + kASmemBytes;
+    unsigned char* smem_b = TS ? raw : raw + kASmemBytes;
     TensorSmemTail& s = *reinterpret_cast<TensorSmemTail*>(raw + kASmemBytes + kTStages * kBStageBytes);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t q0 = blockIdx.x * kTQ;  // may lie past the last query (the odd CTA of the last pair): all rows invalid
@@ -249,7 +268,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
             s.lkeys[r][j] = ~0ull;
         s.thr[r] = make_uint4(0, 1, 0, 2048);  // list not full: every valid row (|d| < 2048) passes, padding rows do not
     }
-    {
+    if (!TS) {
         const uint32_t* q32 = reinterpret_cast<const uint32_t*>(p.queries);
         for (int idx = tid; idx < kTQ * 64; idx += kTThreads) {
             int r = idx & (kTQ - 1), k16 = idx >> 7;
@@ -294,6 +313,39 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = s.tmem_base;
+    if (TS) {
+        // the query tile goes to tensor memory: thread = query = TMEM lane, 4 columns per 16-byte K piece in the piece
+        // order of the database operand, written 32 columns (8 pieces = 128 fingerprint bits) at a time
+        if (warp < kTEpiWarps) {
+            const uint32_t q = q0 + (uint32_t)tid;
+            const uint4* qrow = p.queries + (size_t)q * 8;
+#pragma unroll 1
+            for (int c = 0; c < 8; ++c) {
+                const uint4 v = q < p.query_count ? __ldg(qrow + c) : make_uint4(0, 0, 0, 0);
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+                uint32_t r[32];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint4 u = unpack_half_query(w[j >> 1], j & 1);
+                    r[j * 4 + 0] = u.x, r[j * 4 + 1] = u.y, r[j * 4 + 2] = u.z, r[j * 4 + 3] = u.w;
+                }
+                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(256 + c * 32);
+                asm volatile(
+                    "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                    "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+                    "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+                    ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
+                      "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
+                      "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
+                      "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+                    : "memory");
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+    }
     const bool dbg = p.debug_cycles != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
     unsigned long long dbg_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const long long dbg_start = clock64();
@@ -377,13 +429,13 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
 #pragma unroll
                 for (int h = 0; h < 8 / kTPieces; ++h) {  // K piece c * 8 + h * kTPieces + j  <->  A piece of the same index
                     const uint64_t g = t * kTSteps + c * (8 / kTPieces) + h;
-                    const int st = (int)(g & (kTStages - 1));
+                    const int st = (int)(g % STAGES);
                     uint4 u[kTPieces];
 #pragma unroll
                     for (int j = 0; j < kTPieces; ++j)
                         u[j] = unpack_half_db(w[(h * kTPieces + j) >> 1], j & 1);
-                    RB_TICK(1, mbar_wait(&s.empty[st], (uint32_t)(((g / kTStages) & 1) ^ 1)));
-                    unsigned char* dst = my_b + st * kBStageBytes;
+                    RB_TICK(1, mbar_wait(&s.empty[st], (uint32_t)(((g / STAGES) & 1) ^ 1)));
+                    unsigned char* dst = my_b + st * STAGE_BYTES;
 #pragma unroll
                     for (int j = 0; j < kTPieces; ++j)
                         *reinterpret_cast<uint4*>(dst + j * kLBO) = u[j];
@@ -409,15 +461,16 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), kLBO, kSBO_A);
         const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), kLBO, SBO_B);
         for (uint64_t t = 0; t < n_tiles && rank == 0; ++t) {  // in a pair only the leader CTA issues
-            const int a = (int)(t & 1);
+            const int a = TS ? 0 : (int)(t & 1);               // TS: one accumulator, one tile in flight
+            const uint32_t tph = TS ? (uint32_t)(t & 1) : (uint32_t)((t >> 1) & 1);
             if (PAIR)
-                mbar_wait_cluster(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
+                mbar_wait_cluster(&s.tmem_empty[a], tph ^ 1);
             else
-                RB_TICK(1, mbar_wait(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1)));
+                RB_TICK(1, mbar_wait(&s.tmem_empty[a], tph ^ 1));
             tc_fence_after();
             for (int c = 0; c < STEPS; ++c) {
                 const uint64_t g = t * STEPS + c;
-                const int st = (int)(g & (STAGES - 1));
+                const int st = (int)(g % STAGES);
                 if (PAIR)
                     mbar_wait_cluster(&s.full[st], (uint32_t)((g / STAGES) & 1));
                 else
@@ -431,6 +484,9 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                         uint64_t bd = b_desc0 + (uint64_t)((st * STAGE_BYTES + j * 2 * kLBO) >> 4);
                         if (PAIR)
                             tc_mma_i8_pair(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8Pair, (uint32_t)((c | j) != 0));
+                        else if (TS)
+                            tc_mma_i8_ts(tmem_base, tmem_base + (uint32_t)(256 + (c * PIECES + j * 2) * 4), bd, kIdescI8,
+                                         (uint32_t)((c | j) != 0));
                         else
                             tc_mma_i8(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8, (uint32_t)((c | j) != 0));
                     }
@@ -455,13 +511,15 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         const bool share_bounds = smem_lists && p.bounds != nullptr;  // bound word: d bits << 32 | chunk << 23 | i << 12 | u
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;
-            const int a = (int)(t & 1);
+            const int a = (int)(t & 1);            // popcount side array of this tile
+            const int acc_i = TS ? 0 : a;          // accumulator stage (TS: the only one)
+            const uint32_t acc_ph = TS ? (uint32_t)(t & 1) : (uint32_t)((t >> 1) & 1);
             if (PAIR) {
                 mbar_wait_cluster(&s.pd_full[a], (uint32_t)((t >> 1) & 1));
-                mbar_wait_cluster(&s.tmem_full[a], (uint32_t)((t >> 1) & 1));
+                mbar_wait_cluster(&s.tmem_full[acc_i], acc_ph);
             } else {
                 RB_TICK(0, mbar_wait(&s.pd_full[a], (uint32_t)((t >> 1) & 1)));
-                RB_TICK(1, mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1)));
+                RB_TICK(1, mbar_wait(&s.tmem_full[acc_i], acc_ph));
             }
             tc_fence_after();
             // Shared bounds.  Every CTA starts with empty lists, and until a list is full and tight nearly every pair
@@ -487,7 +545,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
             // measured 5 % SLOWER: 128 registers with spills, and the read competes with the MMAs' accumulator traffic.)
             for (int b = kTD / 32 - 1; b >= 0; --b) {
                 uint32_t acc[32];
-                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * kTD + b * 32);
+                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(acc_i * kTD + b * 32);
                 long long te0 = dbg ? clock64() : 0;
                 RB_TMEM_LD32(acc, taddr);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -499,7 +557,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                         if (PAIR)
                             mbar_arrive_cluster(map_to_cta(&s.tmem_empty[a], 0));
                         else
-                            mbar_arrive(&s.tmem_empty[a]);
+                            mbar_arrive(&s.tmem_empty[acc_i]);
                     }
                 }
                 // exact integer filter, 3 instructions per pair: the pair passes iff

@@ -14,11 +14,11 @@ from rad_b200.index import Index
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["popc", "i8", "i8x2"])
+@pytest.fixture(autouse=True, params=["popc", "i8", "i8x2", "i8ts"])
 def exact_kernel(request, monkeypatch):
     """Every test of this module runs against ALL exact-search kernels: the POPC-pipe kernel, the tcgen05 int8
-    tensor-core kernel and its CTA-pair (cta_group::2) form (rad_b200/csrc/exact_i8_kernels.cuh); the library reads
-    RB_EXACT_KERNEL on every call."""
+    tensor-core kernel, its CTA-pair (cta_group::2) form and its form with the query operand in tensor memory
+    (rad_b200/csrc/exact_i8_kernels.cuh); the library reads RB_EXACT_KERNEL on every call."""
     monkeypatch.setenv("RB_EXACT_KERNEL", request.param)
     return request.param
 
