@@ -38,9 +38,10 @@ def n_centres(n_total: int) -> int:
     return max(1000, n_total // 100)
 
 
-def centre_table(seed: int, n_total: int, ndim: int = NDIM) -> np.ndarray:
-    """uint8 [C, ndim/8] packed cluster centres (host-side numpy; uploaded as-is for the device generator)."""
-    c = n_centres(n_total)
+def centre_table(seed: int, n_total: int, ndim: int = NDIM, *, count: int | None = None) -> np.ndarray:
+    """uint8 [C, ndim/8] packed cluster centres (host-side numpy; uploaded as-is for the device generator).
+    ``count`` overrides C = max(1000, n_total / 100): the first C rows of the table do not depend on C."""
+    c = n_centres(n_total) if count is None else int(count)
     rng = np.random.default_rng([seed, 0xC3])
     p = rng.uniform(0.03, 0.08, size=(c, 1)).astype(np.float32)
     out = np.empty((c, ndim // 8), dtype=np.uint8)
@@ -58,9 +59,27 @@ def row_assignment(rows: np.ndarray, seed: int, c: int) -> np.ndarray:
     return (h % np.uint64(c)).astype(np.int64)
 
 
+def source_rows(rows: np.ndarray, dup_fold: int = 0, dup_start: int = 0, dup_rows: int = 0) -> np.ndarray:
+    """The row whose bits row r carries: r itself, except inside the duplicate region [dup_start, dup_start + dup_rows)
+    where every run of ``dup_fold`` consecutive rows repeats the first row of the run (exact duplicates, d = 0)."""
+    rows = rows.astype(np.uint64)
+    if dup_fold > 1 and dup_rows:
+        inside = (rows >= np.uint64(dup_start)) & (rows < np.uint64(dup_start + dup_rows))
+        rel = rows - np.uint64(dup_start)
+        rows = np.where(inside, np.uint64(dup_start) + rel - rel % np.uint64(dup_fold), rows)
+    return rows
+
+
 def clustered_fingerprints(n: int, seed: int = 0, *, start: int = 0, n_total: int | None = None,
-                           ndim: int = NDIM, edge_cases: bool = True, centres: np.ndarray | None = None) -> np.ndarray:
-    """Rows [start, start + n) of the synthetic set of ``n_total`` rows (default ``start + n``) -> uint8 [n, ndim/8]."""
+                           ndim: int = NDIM, edge_cases: bool = True, centres: np.ndarray | None = None,
+                           rows_per_centre: int = 0, dup_fold: int = 0, dup_start: int = 0,
+                           dup_rows: int = 0) -> np.ndarray:
+    """Rows [start, start + n) of the synthetic set of ``n_total`` rows (default ``start + n``) -> uint8 [n, ndim/8].
+
+    ``rows_per_centre`` > 0 selects the ANALOGUE-SERIES order: row r belongs to centre (r // rows_per_centre) mod C, so
+    the rows of one cluster are contiguous in insertion order (a build batch then holds whole clusters whose members
+    have never seen each other); 0 = the hashed assignment.  ``dup_fold`` / ``dup_start`` / ``dup_rows`` plant runs
+    of exact duplicates (``source_rows``)."""
     if n_total is None:
         n_total = start + n
     if centres is None:
@@ -72,19 +91,50 @@ def clustered_fingerprints(n: int, seed: int = 0, *, start: int = 0, n_total: in
         base = np.uint64(seed) * _GOLD
         for lo in range(0, n, _ROWS_PER_CHUNK):
             hi = min(n, lo + _ROWS_PER_CHUNK)
-            rows = np.arange(start + lo, start + hi, dtype=np.uint64)
+            rows = source_rows(np.arange(start + lo, start + hi, dtype=np.uint64), dup_fold, dup_start, dup_rows)
             h = _mix64(base + ((rows[:, None] << np.uint64(10)) | bit_ids))
             keep = (h & np.uint64(0xFFFF)) >= np.uint64(KEEP_T)
             noise = ((h >> np.uint64(16)) & np.uint64(0xFFFF)) < np.uint64(NOISE_T)
-            cbits = np.unpackbits(centres[row_assignment(rows, seed, c)], axis=1).astype(bool)
+            if rows_per_centre > 0:
+                assign = ((rows // np.uint64(rows_per_centre)) % np.uint64(c)).astype(np.int64)
+            else:
+                assign = row_assignment(rows, seed, c)
+            cbits = np.unpackbits(centres[assign], axis=1).astype(bool)
             out[lo:hi] = np.packbits((cbits & keep) | noise, axis=1)
     if edge_cases and n_total >= 3:
         if start <= 0 < start + n:
             out[0 - start] = 0
         if start <= 1 < start + n:
             out[1 - start] = clustered_fingerprints(1, seed, start=2, n_total=n_total, ndim=ndim,
-                                                    edge_cases=False, centres=centres)[0]
+                                                    edge_cases=False, centres=centres,
+                                                    rows_per_centre=rows_per_centre, dup_fold=dup_fold,
+                                                    dup_start=dup_start, dup_rows=dup_rows)[0]
     return out
+
+
+def dense_set(n: int, seed: int = 0, **kw) -> np.ndarray:
+    """The ROUTABLE set (SURVEY.md §6 probe): a fixed table of 1000 centres whatever n, hashed assignment -- n/1000 rows
+    per cluster; the reference graph reaches recall@10 0.99 at ef=64 on it at 100 k rows."""
+    return clustered_fingerprints(n, seed, centres=centre_table(seed, n, count=1000), **kw)
+
+
+ANALOGUE_ROWS_PER_CENTRE = 200
+ANALOGUE_DUP_FOLD = 400
+
+
+def analogue_params(n_total: int) -> dict:
+    """Generator arguments of the ADVERSARIAL analogue-series set: n/200 centres, the 200 rows of a centre contiguous
+    in insertion order, and 1/50 of the rows (from n/2 on) in runs of 400 exact duplicates."""
+    dup_rows = (n_total // 50) // ANALOGUE_DUP_FOLD * ANALOGUE_DUP_FOLD
+    return dict(rows_per_centre=ANALOGUE_ROWS_PER_CENTRE, dup_fold=ANALOGUE_DUP_FOLD,
+                dup_start=(n_total // 2) // ANALOGUE_ROWS_PER_CENTRE * ANALOGUE_ROWS_PER_CENTRE, dup_rows=dup_rows)
+
+
+def analogue_set(n: int, seed: int = 0, *, start: int = 0, n_total: int | None = None, **kw) -> np.ndarray:
+    n_total = start + n if n_total is None else n_total
+    centres = centre_table(seed, n_total, count=max(1, n_total // ANALOGUE_ROWS_PER_CENTRE))
+    return clustered_fingerprints(n, seed, start=start, n_total=n_total, centres=centres,
+                                  **analogue_params(n_total), **kw)
 
 
 def queries_from_db(db: np.ndarray, q: int, seed: int = 1) -> np.ndarray:

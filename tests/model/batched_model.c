@@ -37,6 +37,7 @@ typedef struct {
     uint32_t m, m0, ef;
     uint32_t bloom_bits_log2;
     uint32_t growth_den, batch_max;
+    uint32_t batch_k;     /* batch-mates offered to every (node, level) task; 0 = none */
     uint64_t n, cap;
     const uint8_t* vecs;  /* borrowed: cap x 128 bytes */
     int16_t* levels;
@@ -84,7 +85,7 @@ static inline uint32_t row_count(const uint32_t* row, uint32_t width) {
 }
 
 BM_EXPORT bm_index* bm_new(uint32_t m, uint32_t ef, uint32_t bloom_bits_log2, uint32_t growth_den, uint32_t batch_max,
-                           const uint8_t* vecs, const int16_t* levels, uint64_t n) {
+                           uint32_t batch_k, const uint8_t* vecs, const int16_t* levels, uint64_t n) {
     bm_index* ix = (bm_index*)calloc(1, sizeof(bm_index));
     ix->m = m;
     ix->m0 = 2 * m;
@@ -92,6 +93,7 @@ BM_EXPORT bm_index* bm_new(uint32_t m, uint32_t ef, uint32_t bloom_bits_log2, ui
     ix->bloom_bits_log2 = bloom_bits_log2;
     ix->growth_den = growth_den;
     ix->batch_max = batch_max;
+    ix->batch_k = batch_k > 64 ? 64 : batch_k;
     ix->cap = n;
     ix->vecs = vecs;
     ix->levels = (int16_t*)malloc(n * sizeof(int16_t));
@@ -364,6 +366,12 @@ BM_EXPORT void bm_build(bm_index* ix, uint64_t upto, uint64_t max_batches) {
                 acc += (size_t)((l < ix->max_level ? l : ix->max_level) + 1);
             }
         }
+        /* phase 1 (search_kernel of the build): every task's ef-bounded search against the frozen graph; the sorted
+         * candidate lists are kept per task.  The search of the next level down starts from the closest entry found
+         * in the OLD graph (batch-mates join only in phase 3). */
+        const uint32_t ef = ix->ef;
+        uint64_t* lists = (uint64_t*)malloc((ntasks ? ntasks : 1) * (size_t)ef * 8);
+        uint32_t* lens = (uint32_t*)malloc((ntasks ? ntasks : 1) * 4);
         uint64_t dsum = 0, esum = 0;
 #pragma omp parallel reduction(+ : dsum, esum)
         {
@@ -372,7 +380,6 @@ BM_EXPORT void bm_build(bm_index* ix, uint64_t upto, uint64_t max_batches) {
             sc.expanded = (uint8_t*)malloc(ix->ef + 2);
             sc.bloom = (uint32_t*)malloc((1u << ix->bloom_bits_log2) / 8);
             sc.distances = sc.expansions = 0;
-            uint64_t* sel = (uint64_t*)malloc((ix->ef + 2) * 8);
 #pragma omp for schedule(dynamic, 16)
             for (uint64_t t = 0; t < b; ++t) {
                 uint32_t slot = (uint32_t)(s + t);
@@ -404,8 +411,114 @@ BM_EXPORT void bm_build(bm_index* ix, uint64_t upto, uint64_t max_batches) {
                 }
                 size_t task = task_base[t];
                 for (int l = lq < ix->max_level ? lq : ix->max_level; l >= 0; --l, ++task) {
-                    beam_search(ix, &sc, q, cur, cur_bits, l, ix->ef);
-                    uint32_t ns = select_neighbors(ix, sc.list, sc.len, ix->m, sel, &sc.distances);
+                    beam_search(ix, &sc, q, cur, cur_bits, l, ef);
+                    memcpy(lists + task * ef, sc.list, (size_t)sc.len * 8);
+                    lens[task] = sc.len;
+                    cur = (uint32_t)sc.list[0];
+                    cur_bits = (uint32_t)(sc.list[0] >> 32);
+                }
+            }
+            dsum += sc.distances;
+            esum += sc.expansions;
+            free(sc.list);
+            free(sc.expanded);
+            free(sc.bloom);
+        }
+        /* phase 2 (the batch tile): the nodes of a batch never meet in the frozen graph, so every task is offered its
+         * batch_k nearest EARLIER BATCH-MATES.  "Earlier" is the order in which the kernels hand out the work of a
+         * batch: nodes with more levels to search first, equal counts by ascending slot (a stable counting sort) --
+         * so every batch-mate in front of a node exists on all of that node's levels.  Per task: the exact top-batch_k
+         * of the rows in front of the node by (distance ascending, position DESCENDING) -- the exact-search order --
+         * among the rows strictly closer than the task's worst list entry when its list is full (anything else could
+         * not enter the list). */
+        const uint32_t bk = ix->batch_k;
+        uint64_t* mates = NULL;  /* per task: bk keys (distance bits << 32 | slot), ascending; ~0 padding */
+        if (bk) {
+            mates = (uint64_t*)malloc((ntasks ? ntasks : 1) * (size_t)bk * 8);
+            uint32_t* order = (uint32_t*)malloc(b * 4); /* position -> node of the batch */
+            {
+                size_t count[64] = {0}, first[64];
+                for (uint64_t t = 0; t < b; ++t) {
+                    int l = ix->levels[s + t];
+                    ++count[(l < ix->max_level ? l : ix->max_level) & 63];
+                }
+                size_t acc = 0;
+                for (int l = 63; l >= 0; --l) {
+                    first[l] = acc;
+                    acc += count[l];
+                }
+                for (uint64_t t = 0; t < b; ++t) {
+                    int l = ix->levels[s + t];
+                    order[first[(l < ix->max_level ? l : ix->max_level) & 63]++] = (uint32_t)t;
+                }
+            }
+#pragma omp parallel for schedule(dynamic, 16) reduction(+ : dsum)
+            for (uint64_t pos = 0; pos < b; ++pos) {
+                const uint64_t t = order[pos];
+                uint32_t slot = (uint32_t)(s + t);
+                const uint8_t* q = ix->vecs + (size_t)slot * 128;
+                int lq = ix->levels[slot];
+                size_t task = task_base[t];
+                uint64_t top[64]; /* keys: distance bits << 32 | ~position, ascending */
+                for (int l = lq < ix->max_level ? lq : ix->max_level; l >= 0; --l, ++task) {
+                    uint32_t tau = lens[task] == ef ? (uint32_t)(lists[task * ef + ef - 1] >> 32) : 0xFFFFFFFFu;
+                    uint32_t nt = 0;
+                    for (uint64_t p2 = 0; p2 < pos; ++p2) {
+                        uint32_t bits = dist_bits(q, ix->vecs + (size_t)(s + order[p2]) * 128);
+                        dsum++;
+                        if (bits >= tau)
+                            continue;
+                        uint64_t key = ((uint64_t)bits << 32) | (uint32_t)~(uint32_t)p2;
+                        if (nt == bk && key >= top[nt - 1])
+                            continue;
+                        uint32_t at = nt < bk ? nt : nt - 1;
+                        while (at > 0 && top[at - 1] > key) {
+                            top[at] = top[at - 1];
+                            --at;
+                        }
+                        top[at] = key;
+                        if (nt < bk)
+                            ++nt;
+                    }
+                    uint64_t* out = mates + task * bk;
+                    for (uint32_t j = 0; j < nt; ++j)
+                        out[j] = (top[j] & 0xFFFFFFFF00000000ull) | (uint32_t)(s + order[~(uint32_t)top[j]]);
+                    qsort(out, nt, 8, u64_cmp);
+                    for (uint32_t j = nt; j < bk; ++j)
+                        out[j] = ~0ull;
+                }
+            }
+            free(order);
+        }
+        /* phase 3 (select_kernel): batch-mates merged into the list (the ef smallest keys survive), the heuristic,
+         * forward links and the reverse-link records */
+#pragma omp parallel reduction(+ : dsum)
+        {
+            uint64_t* merged = (uint64_t*)malloc((ef + 2) * 8);
+            uint64_t* sel = (uint64_t*)malloc((ef + 2) * 8);
+            uint64_t nd = 0;
+#pragma omp for schedule(dynamic, 16)
+            for (uint64_t t = 0; t < b; ++t) {
+                uint32_t slot = (uint32_t)(s + t);
+                int lq = ix->levels[slot];
+                size_t task = task_base[t];
+                for (int l = lq < ix->max_level ? lq : ix->max_level; l >= 0; --l, ++task) {
+                    uint32_t len = lens[task];
+                    memcpy(merged, lists + task * ef, (size_t)len * 8);
+                    for (uint32_t j = 0; bk && j < bk && mates[task * bk + j] != ~0ull; ++j) {
+                        uint64_t key = mates[task * bk + j];
+                        if (len == ef && key >= merged[ef - 1])
+                            continue;
+                        uint32_t pos = len < ef ? len : ef - 1;
+                        while (pos > 0 && merged[pos - 1] > key) {
+                            merged[pos] = merged[pos - 1];
+                            --pos;
+                        }
+                        merged[pos] = key;
+                        if (len < ef)
+                            ++len;
+                    }
+                    uint32_t ns = select_neighbors(ix, merged, len, ix->m, sel, &nd);
                     uint32_t width;
                     uint32_t* mine = row_of(ix, slot, l, &width);
                     for (uint32_t j = 0; j < width; ++j)
@@ -420,17 +533,15 @@ BM_EXPORT void bm_build(bm_index* ix, uint64_t upto, uint64_t max_batches) {
                             p->val = 0;
                         }
                     }
-                    cur = (uint32_t)sc.list[0];
-                    cur_bits = (uint32_t)(sc.list[0] >> 32);
                 }
             }
-            dsum += sc.distances;
-            esum += sc.expansions;
-            free(sc.list);
-            free(sc.expanded);
-            free(sc.bloom);
+            dsum += nd;
+            free(merged);
             free(sel);
         }
+        free(lists);
+        free(lens);
+        free(mates);
         ix->computed_distances += dsum;
         ix->expansions += esum;
         /* drop the padding pairs, then merge the reverse links */

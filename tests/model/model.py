@@ -29,7 +29,8 @@ def lib() -> C.CDLL:
                                    "-fvisibility=hidden", "-o", so, src, "-lm"])
         L = C.CDLL(so)
         L.bm_new.restype = C.c_void_p
-        L.bm_new.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _u8p, _i16p, C.c_uint64]
+        L.bm_new.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _u8p, _i16p,
+                             C.c_uint64]
         L.bm_free.argtypes = [C.c_void_p]
         L.bm_build.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64]
         L.bm_search.argtypes = [C.c_void_p, _u8p, C.c_uint64, C.c_uint32, C.c_uint32, _u32p, _f32p, _i64p]
@@ -45,14 +46,14 @@ def lib() -> C.CDLL:
 
 class BatchedModel:
     def __init__(self, vecs: np.ndarray, levels: np.ndarray, *, connectivity=8, expansion_add=400,
-                 bloom_bits_log2=15, growth_den=8, batch_max=65536):
+                 bloom_bits_log2=15, growth_den=8, batch_max=65536, batch_k=16):
         self.vecs = np.ascontiguousarray(vecs, dtype=np.uint8)
         assert self.vecs.shape[1] == 128
         self.levels = np.ascontiguousarray(levels, dtype=np.int16)
         self.m = connectivity
         self.m0 = 2 * connectivity
         self._h = C.c_void_p(lib().bm_new(connectivity, expansion_add, bloom_bits_log2, growth_den, batch_max,
-                                          self.vecs, self.levels, len(self.levels)))
+                                          batch_k, self.vecs, self.levels, len(self.levels)))
 
     def __del__(self):
         if getattr(self, "_h", None):
