@@ -50,6 +50,7 @@ typedef struct rb_init_options {
     uint32_t batch_max;        /* upper bound of a batch; 0 -> 65536                                          */
     uint32_t bloom_bits_log2;  /* visited filter size per traversal (bits, log2); 0 -> 15                     */
     uint32_t debug_max_batches;/* stop an rb_add after this many batches (0 = unlimited); tests only          */
+    uint32_t no_batch_tile;    /* 1: skip the batch tile (the nodes of a batch stay blind to each other); A/B only */
 } rb_init_options_t;
 
 /* per-level statistics: usearch python/lib.cpp:1007-1013 (IndexStats), index.hpp:3087-3179 */
@@ -75,10 +76,12 @@ typedef struct rb_counters {
     uint64_t kernel_launches;      /* CUDA kernels of this library launched                                   */
     double device_ms;              /* CUDA-event time of the device work, on the library's stream             */
     /* with RB_FLAG_TIME_KERNELS: summed CUDA-event durations of each kernel class of the last rb_add */
-    double insert_ms;              /* insert_kernel (beam search + heuristic select + forward links)          */
+    double insert_ms;              /* insert_search_kernel (greedy descent + ef-bounded searches of a batch)  */
     double sort_ms;                /* radix sort of the (level, target) reverse pairs                         */
     double reverse_ms;             /* reverse_link_kernel                                                     */
-    uint64_t insert_launches;      /* insert_kernel launches (= batches that did graph work)                  */
+    uint64_t insert_launches;      /* insert_search_kernel launches (= batches that did graph work)           */
+    double tile_ms;                /* the batch tile (exact nearest earlier batch-mates, tensor cores)        */
+    double select_ms;              /* insert_select_kernel (merge batch-mates, heuristic, forward links)      */
 } rb_counters_t;
 
 /* ---------------------------------------------------------------- lifetime: python/lib.cpp:116-147, index.py:1154-1162 */

@@ -25,6 +25,7 @@ class InitOptions(C.Structure):
         ("batch_max", C.c_uint32),
         ("bloom_bits_log2", C.c_uint32),
         ("debug_max_batches", C.c_uint32),
+        ("no_batch_tile", C.c_uint32),
     ]
 
 
@@ -47,7 +48,8 @@ class Metadata(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("computed_distances", C.c_uint64), ("visited_members", C.c_uint64), ("batches", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("device_ms", C.c_double), ("insert_ms", C.c_double),
-                ("sort_ms", C.c_double), ("reverse_ms", C.c_double), ("insert_launches", C.c_uint64)]
+                ("sort_ms", C.c_double), ("reverse_ms", C.c_double), ("insert_launches", C.c_uint64),
+                ("tile_ms", C.c_double), ("select_ms", C.c_double)]
 
 
 PROGRESS = C.CFUNCTYPE(C.c_int, C.c_uint64, C.c_uint64, C.c_void_p)

@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -95,6 +96,15 @@ struct DeviceState {
     uint64_t* pair_keys[2] = {nullptr, nullptr};
     uint64_t* pair_vals[2] = {nullptr, nullptr};
     size_t pair_cap = 0;
+    // per-(level, position) task arrays of one batch (hnsw_kernels.cuh: InsertParams)
+    uint64_t* task_lists = nullptr;
+    uint32_t* task_lens = nullptr;
+    unsigned long long* task_seeds = nullptr;
+    uint64_t* mate_keys = nullptr;
+    uint32_t* mate_iu = nullptr;
+    size_t task_cap = 0, task_cap_ef = 0;
+    uint4* batch_fp = nullptr;
+    size_t batch_fp_cap = 0;
     void* sort_tmp = nullptr;
     size_t sort_tmp_bytes = 0;
     unsigned int* work_counters = nullptr;
@@ -103,7 +113,7 @@ struct DeviceState {
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
     cudaStream_t copy_stream = nullptr;  // metadata of the second segment of a large add (build_new_rows)
     cudaEvent_t ev_copy = nullptr;
-    int insert_blocks_per_sm = 0, search_blocks_per_sm = 0;
+    int insert_blocks_per_sm = 0, search_blocks_per_sm = 0, select_blocks_per_sm = 0;
     int insert_variant = 4, search_variant = 4;
     uint32_t insert_cfg_ef = 0, search_cfg_ef = 0;
     void* scratch = nullptr;  // grow-only arena for query / result staging
@@ -127,6 +137,12 @@ struct DeviceState {
             cudaFree(pair_keys[i]);
             cudaFree(pair_vals[i]);
         }
+        cudaFree(task_lists);
+        cudaFree(task_lens);
+        cudaFree(task_seeds);
+        cudaFree(mate_keys);
+        cudaFree(mate_iu);
+        cudaFree(batch_fp);
         cudaFree(sort_tmp);
         cudaFree(work_counters);
         cudaFree(counters);
@@ -293,6 +309,19 @@ std::string upload_graph(rb_index* ix) {
     return {};
 }
 
+rb::GraphView graph_view(rb_index* ix) {
+    rb::GraphView g;
+    g.fp = ix->dev.fp;
+    g.adj0 = ix->dev.adj0;
+    g.adju = ix->dev.adju;
+    g.upper_off = ix->dev.upper_off;
+    g.pc0 = ix->dev.pc0;
+    g.pcu = ix->dev.pcu;
+    g.m = ix->host.m;
+    g.m0 = ix->host.m0;
+    return g;
+}
+
 std::string sync_host(rb_index* ix) {
     if (ix->host_graph_valid)
         return {};
@@ -306,7 +335,20 @@ std::string sync_host(rb_index* ix) {
         RB_CUDA(cudaMemcpyAsync(h.adj0.data(), d.adj0, h.adj0.size() * 4, cudaMemcpyDeviceToHost, d.stream));
     if (!h.adju.empty())
         RB_CUDA(cudaMemcpyAsync(h.adju.data(), d.adju, h.adju.size() * 4, cudaMemcpyDeviceToHost, d.stream));
-    RB_CUDA(cudaStreamSynchronize(d.stream));
+    // the edge counts per level travel with the adjacency (HostIndex: per-level metadata)
+    unsigned long long* d_edges = nullptr;
+    unsigned long long edges[rb::kMaxLevels] = {0};
+    if (n) {
+        RB_CUDA(cudaMalloc(&d_edges, sizeof(edges)));
+        RB_CUDA(cudaMemsetAsync(d_edges, 0, sizeof(edges), d.stream));
+        const unsigned grid = (unsigned)std::min<size_t>((n + 255) / 256, (size_t)d.sm_count * 8);
+        rb::edge_count_kernel<<<grid, 256, 0, d.stream>>>(graph_view(ix), d.levels, (uint32_t)n, d_edges);
+        RB_CUDA(cudaMemcpyAsync(edges, d_edges, sizeof(edges), cudaMemcpyDeviceToHost, d.stream));
+    }
+    cudaError_t se = cudaStreamSynchronize(d.stream);
+    cudaFree(d_edges);
+    RB_CUDA(se);
+    h.set_level_edges(std::vector<uint64_t>(edges, edges + rb::kMaxLevels));
     ix->host_graph_valid = true;
     return {};
 }
@@ -322,6 +364,8 @@ struct Batch {
     int32_t max_level;
     uint32_t tasks;
     uint32_t tasks_bound;  // size + sum of levels: known after pass 1, >= tasks
+    uint32_t levels;       // levels with work in this batch: 1 + max over its nodes of min(level, max_level)
+    uint32_t level_cnt[rb::kMaxLevels];  // nodes of the batch that have a task on level l = a prefix of the work order
 };
 
 // run f(i) for i in [0, count) on up to 16 host threads (static interleaved split; f must be thread-safe per i)
@@ -355,7 +399,7 @@ void plan_batch_bounds(rb_index* ix, size_t old_size, std::vector<int16_t> const
         if (ix->opts.debug_max_batches && batches.size() >= ix->opts.debug_max_batches)
             break;
         if (s == 0) {
-            batches.push_back(Batch{0, 1, 0, -1, 0, 0});  // the first node only becomes the entry point
+            batches.push_back(Batch{0, 1, 0, -1, 0, 0, 0, {0}});  // the first node only becomes the entry point
             entry = 0;
             max_level = all_levels[0];
             s = 1;
@@ -378,7 +422,7 @@ void plan_batch_bounds(rb_index* ix, size_t old_size, std::vector<int16_t> const
             }
             bound += 1u + (uint32_t)all_levels[s + t];
         }
-        batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, 0, bound});
+        batches.push_back(Batch{(uint32_t)s, (uint32_t)b, (uint32_t)entry, max_level, 0, bound, 0, {0}});
         if (raised)
             for (size_t t = 0; t < b; ++t)
                 if (all_levels[s + t] > max_level) {
@@ -416,12 +460,40 @@ void plan_batch_tasks(size_t old_size, std::vector<int16_t> const& all_levels, s
         for (int l = 63; l >= 0; --l) {
             start[l] = acc;
             acc += count[l];
+            if (l < rb::kMaxLevels) {
+                bt.level_cnt[l] = (uint32_t)acc;  // nodes with at least l searched levels above level 0
+                if (acc && !bt.levels)
+                    bt.levels = (uint32_t)l + 1;
+            }
         }
         for (size_t t = 0; t < b; ++t) {
             const size_t jobs = (size_t)std::min<int32_t>(all_levels[s0 + t], top);
             task_order[s0 - old_size + start[std::min<size_t>(jobs, 63)]++] = (uint32_t)t;
         }
     });
+}
+
+// the exact-search kernels use more than 48 KB of dynamic shared memory: opt in once per DEVICE (the attribute belongs
+// to the device's context, not to the process)
+std::string configure_exact_kernels() {
+    static std::mutex mu;
+    static bool configured[64] = {false};
+    int dev = 0;
+    RB_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < 64 && configured[dev])
+        return {};
+    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)sizeof(rb::ExactSmem)));
+    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)rb::kTensorSmemBytes));
+    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)rb::kTensorSmemBytes));
+    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)rb::kTensorSmemBytes));
+    if (dev >= 0 && dev < 64)
+        configured[dev] = true;
+    return {};
 }
 
 // resident CTAs per SM that `smem` bytes of dynamic shared memory per CTA allow, quantised to the compiled variants
@@ -454,11 +526,18 @@ std::string configure_traversal_kernels(rb_index* ix) {
         size_t smem = rb::warp_scratch_bytes(ix->host.ef_add, bloom, m) * rb::kWarpsPerBlock;
         d.insert_variant = traversal_variant(smem);
         const void* fn = nullptr;
-        RB_FOR_VARIANT(d.insert_variant, fn = (const void*)rb::insert_kernel<V>);
+        RB_FOR_VARIANT(d.insert_variant, fn = (const void*)rb::insert_search_kernel<V>);
         std::string err = configure_variant(fn, smem, d.insert_blocks_per_sm);
         if (!err.empty())
             return err;
         if (d.insert_blocks_per_sm < 1)
+            return "expansion_add does not fit the shared memory of one SM";
+        err = configure_variant((const void*)rb::insert_select_kernel,
+                                rb::select_scratch_bytes(ix->host.ef_add, m) * rb::kWarpsPerBlock,
+                                d.select_blocks_per_sm);
+        if (!err.empty())
+            return err;
+        if (d.select_blocks_per_sm < 1)
             return "expansion_add does not fit the shared memory of one SM";
         d.insert_cfg_ef = ix->host.ef_add;
     }
@@ -480,19 +559,6 @@ std::string configure_search_kernel(rb_index* ix, uint32_t ef) {
         d.search_cfg_ef = ef;
     }
     return {};
-}
-
-rb::GraphView graph_view(rb_index* ix) {
-    rb::GraphView g;
-    g.fp = ix->dev.fp;
-    g.adj0 = ix->dev.adj0;
-    g.adju = ix->dev.adju;
-    g.upper_off = ix->dev.upper_off;
-    g.pc0 = ix->dev.pc0;
-    g.pcu = ix->dev.pcu;
-    g.m = ix->host.m;
-    g.m0 = ix->host.m0;
-    return g;
 }
 
 // shared tail of rb_add / rb_add_device: the fingerprints of the new rows are already enqueued on the stream
@@ -578,13 +644,48 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         }
         d.pair_cap = cap;
     }
-    // two work counters per batch: insert_kernel's (nodes) at [bi], reverse_link_kernel's (pairs) at [batches + bi]
-    if (2 * batches.size() > d.work_counters_cap) {
+    // the per-task arrays of a batch: candidate lists, their lengths, the batch tile's seeds and answers
+    {
+        size_t max_tasks = 1, max_batch = 1;
+        for (Batch const& b : batches) {
+            max_tasks = std::max(max_tasks, (size_t)b.tasks_bound);
+            max_batch = std::max(max_batch, (size_t)b.size);
+        }
+        if (max_tasks > d.task_cap || h.ef_add > d.task_cap_ef) {
+            const size_t cap = std::max(ceil2(max_tasks), d.task_cap), ef = std::max<size_t>(h.ef_add, d.task_cap_ef);
+            cudaFree(d.task_lists);
+            cudaFree(d.task_lens);
+            cudaFree(d.task_seeds);
+            cudaFree(d.mate_keys);
+            cudaFree(d.mate_iu);
+            d.task_lists = nullptr, d.task_lens = nullptr, d.task_seeds = nullptr, d.mate_keys = nullptr;
+            d.mate_iu = nullptr;
+            d.task_cap = d.task_cap_ef = 0;
+            RB_CUDA(cudaMalloc(&d.task_lists, cap * ef * 8));
+            RB_CUDA(cudaMalloc(&d.task_lens, cap * 4));
+            RB_CUDA(cudaMalloc(&d.task_seeds, cap * 8));
+            RB_CUDA(cudaMalloc(&d.mate_keys, cap * rb::kBatchMates * 8));
+            RB_CUDA(cudaMalloc(&d.mate_iu, cap * rb::kBatchMates * 4));
+            d.task_cap = cap;
+            d.task_cap_ef = ef;
+        }
+        if (max_batch > d.batch_fp_cap) {
+            cudaFree(d.batch_fp);
+            d.batch_fp = nullptr;
+            d.batch_fp_cap = 0;
+            const size_t cap = ceil2(max_batch);
+            RB_CUDA(cudaMalloc(&d.batch_fp, cap * 128));
+            d.batch_fp_cap = cap;
+        }
+    }
+    // three work counters per batch: insert_search_kernel's (nodes) at [bi], reverse_link_kernel's (pairs) at
+    // [batches + bi], insert_select_kernel's (nodes) at [2 batches + bi]
+    if (3 * batches.size() > d.work_counters_cap) {
         cudaFree(d.work_counters);
-        d.work_counters_cap = ceil2(2 * batches.size());
+        d.work_counters_cap = ceil2(3 * batches.size());
         RB_CUDA(cudaMalloc(&d.work_counters, d.work_counters_cap * sizeof(unsigned int)));
     }
-    RB_CUDA(cudaMemsetAsync(d.work_counters, 0, std::max<size_t>(2 * batches.size(), 1) * sizeof(unsigned int),
+    RB_CUDA(cudaMemsetAsync(d.work_counters, 0, std::max<size_t>(3 * batches.size(), 1) * sizeof(unsigned int),
                             d.stream));
     RB_CUDA(cudaMemsetAsync(d.counters, 0, 4 * sizeof(unsigned long long), d.stream));
 
@@ -592,6 +693,10 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     if (!err.empty())
         return err;
     const size_t smem = rb::warp_scratch_bytes(h.ef_add, ix->opts.bloom_bits_log2, h.m) * rb::kWarpsPerBlock;
+    const size_t select_smem = rb::select_scratch_bytes(h.ef_add, h.m) * rb::kWarpsPerBlock;
+    const bool use_mates = !ix->opts.no_batch_tile;
+    if (use_mates && !(err = configure_exact_kernels()).empty())
+        return err;
     const rb::GraphView g = graph_view(ix);
     uint64_t launches = 0;
     size_t inserted = 0;
@@ -599,7 +704,9 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     std::vector<cudaEvent_t> marks;  // progress marks
     size_t next_mark = 0;
     const bool time_kernels = (ix->opts.flags & RB_FLAG_TIME_KERNELS) != 0;
-    std::vector<cudaEvent_t> ticks;  // 4 per batch with graph work: before insert, after insert, after sort, after reverse
+    // 6 per batch with graph work: before search, after search, after the batch tile, after select, after sort,
+    // after reverse
+    std::vector<cudaEvent_t> ticks;
     auto tick = [&]() -> cudaError_t {
         cudaEvent_t ev;
         cudaError_t e = cudaEventCreate(&ev);
@@ -629,12 +736,81 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
             ip.bloom_log2 = ix->opts.bloom_bits_log2;
             ip.work_counter = d.work_counters + bi;
             ip.counters = d.counters;
+            ip.lists = d.task_lists;
+            ip.lens = d.task_lens;
+            ip.seeds = d.task_seeds;
+            ip.mate_keys = d.mate_keys;
+            ip.batch_fp = d.batch_fp;
+            ip.use_mates = use_mates ? 1u : 0u;
+            {
+                uint32_t off = 0;
+                for (int l = 0; l < rb::kMaxLevels; ++l) {
+                    ip.level_off[l] = off;
+                    off += b.level_cnt[l];
+                }
+            }
             unsigned blocks = (unsigned)std::min<size_t>((b.size + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
                                                          (size_t)d.sm_count * d.insert_blocks_per_sm);
             if (time_kernels)
                 RB_CUDA(tick());
             RB_FOR_VARIANT(d.insert_variant,
-                           (rb::insert_kernel<V><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip)));
+                           (rb::insert_search_kernel<V><<<blocks, rb::kWarpsPerBlock * 32, smem, d.stream>>>(ip)));
+            ++launches;
+            if (time_kernels)
+                RB_CUDA(tick());
+            if (use_mates) {
+                // the batch tile: exact nearest EARLIER batch-mates of every task, all levels in one launch
+                rb::ExactParams ep{};
+                ep.db = ep.queries = d.batch_fp;
+                ep.rows = b.size;
+                ep.slot_base = 0;
+                ep.query_count = b.size;
+                ep.k = rb::kBatchMates;
+                ep.chunks = 1;
+                ep.chunk_rows = ((uint64_t)b.size + rb::kTD - 1) / rb::kTD * rb::kTD;
+                ep.partial_keys = d.mate_keys;
+                ep.partial_iu = d.mate_iu;
+                ep.bounds = d.task_seeds;
+                ep.debug_cycles = nullptr;
+                static unsigned long long* tile_dbg = nullptr;
+                const bool tile_debug = std::getenv("RB_TILE_DEBUG") && bi + 2 == batches.size();
+                if (tile_debug) {
+                    if (!tile_dbg)
+                        RB_CUDA(cudaMalloc(&tile_dbg, 32 * sizeof(unsigned long long)));
+                    RB_CUDA(cudaMemsetAsync(tile_dbg, 0, 32 * sizeof(unsigned long long), d.stream));
+                    ep.debug_cycles = tile_dbg;
+                }
+                ep.tri = 1;
+                for (int l = 0; l < rb::kMaxLevels; ++l) {
+                    ep.tri_cnt[l] = b.level_cnt[l];
+                    ep.tri_off[l] = ip.level_off[l];
+                }
+                dim3 grid((unsigned)((b.size + rb::kTQ - 1) / rb::kTQ), b.levels);
+                rb::exact_topk_i8_kernel_t<0><<<grid, rb::kTThreads, rb::kTensorSmemBytes, d.stream>>>(ep);
+                ++launches;
+                if (tile_debug) {
+                    unsigned long long hh[32];
+                    RB_CUDA(cudaStreamSynchronize(d.stream));
+                    RB_CUDA(cudaMemcpy(hh, tile_dbg, sizeof(hh), cudaMemcpyDeviceToHost));
+                    double tt = (double)std::max<unsigned long long>(hh[31], 1);
+                    fprintf(stderr, "[rb tile] batch %zu size %u: longest CTA tiles=%llu, cycles per tile: producer %.0f (gload %.0f, "
+                                    "wait empty %.0f, wait pd_empty %.0f) mma %.0f (wait tmem_empty %.0f, wait full %.0f) "
+                                    "epilogue %.0f (wait pd_full %.0f, wait tmem_full %.0f, tmem ld %.0f, filter %.0f, slow %.0f, "
+                                    "lane-0 inserts/tile %.1f; whole CTA: %llu filter hits, %llu insertions)\n", bi, b.size, hh[31], hh[0] / tt, hh[1] / tt, hh[2] / tt, hh[3] / tt,
+                            hh[10] / tt, hh[12] / tt, hh[13] / tt, hh[20] / tt, hh[21] / tt, hh[22] / tt, hh[23] / tt, hh[24] / tt,
+                            hh[26] / tt, hh[28] / tt, hh[29], hh[30]);
+                }
+            }
+            if (time_kernels)
+                RB_CUDA(tick());
+            {
+                rb::InsertParams sp = ip;
+                sp.work_counter = d.work_counters + 2 * batches.size() + bi;
+                unsigned sblocks = (unsigned)std::min<size_t>((b.size + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
+                                                              (size_t)d.sm_count * d.select_blocks_per_sm);
+                rb::insert_select_kernel<<<sblocks, rb::kWarpsPerBlock * 32, select_smem, d.stream>>>(sp);
+                ++launches;
+            }
             if (time_kernels)
                 RB_CUDA(tick());
             const size_t pairs = (size_t)b.tasks * h.m;
@@ -654,9 +830,9 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
             if (time_kernels)
                 RB_CUDA(tick());
             rb::reverse_link_kernel<<<rblocks, rb::kWarpsPerBlock * 32, 0, d.stream>>>(rp);
+            ++launches;  // (the radix-sort passes between the two are library code and not counted)
             if (time_kernels)
                 RB_CUDA(tick());
-            launches += 2 + 4;  // ours + the radix-sort passes over 40 key bits (library code)
             RB_CUDA(cudaGetLastError());
         }
         inserted += b.size;
@@ -731,6 +907,8 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
         h.max_level = top;
         h.entry = top_slot;
         h.note_new_keys(keys, count);
+        h.note_new_levels(old_size, new_levels.data(), count);
+        h.invalidate_level_edges();
     };
     const bool early = !progress && !cancelled && inserted == n;
     pt.mark("  launch loop");
@@ -775,17 +953,21 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     ix->last.batches = batches.size();
     ix->last.kernel_launches = launches;
     ix->last.device_ms = ms;
-    ix->last.insert_ms = ix->last.sort_ms = ix->last.reverse_ms = 0;
+    ix->last.insert_ms = ix->last.sort_ms = ix->last.reverse_ms = ix->last.tile_ms = ix->last.select_ms = 0;
     ix->last.insert_launches = 0;
-    for (size_t t = 0; t + 3 < ticks.size(); t += 4) {
-        float a = 0, b2 = 0, c = 0;
-        cudaEventElapsedTime(&a, ticks[t], ticks[t + 1]);
-        cudaEventElapsedTime(&b2, ticks[t + 1], ticks[t + 2]);
-        cudaEventElapsedTime(&c, ticks[t + 2], ticks[t + 3]);
-        ix->last.insert_ms += a;
-        ix->last.sort_ms += b2;
-        ix->last.reverse_ms += c;
+    for (size_t t = 0; t + 5 < ticks.size(); t += 6) {
+        float dt[5] = {0, 0, 0, 0, 0};
+        for (int j = 0; j < 5; ++j)
+            cudaEventElapsedTime(&dt[j], ticks[t + j], ticks[t + j + 1]);
+        ix->last.insert_ms += dt[0];
+        ix->last.tile_ms += dt[1];
+        ix->last.select_ms += dt[2];
+        ix->last.sort_ms += dt[3];
+        ix->last.reverse_ms += dt[4];
         ix->last.insert_launches += 1;
+        if (pt.on && (t + 11 >= ticks.size() || std::getenv("RB_BATCH_TIMING")))  // the last batch (or every batch)
+            std::fprintf(stderr, "[rb batch] %zu: search %.3f  tile %.3f  select %.3f  sort %.3f  reverse %.3f ms\n",
+                         t / 6, dt[0], dt[1], dt[2], dt[3], dt[4]);
     }
     for (cudaEvent_t ev : ticks)
         cudaEventDestroy(ev);
@@ -836,12 +1018,19 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
     h.draw_levels(n, new_levels);
     pt.mark("device ready + level stream");
     uint64_t upper = h.upper_off[old_size];
-    for (size_t i = 0; i < n; ++i)
+    int16_t top_new = 0;
+    for (size_t i = 0; i < n; ++i) {
         upper += (uint64_t)new_levels[i];
-    if (upper >= (1ull << 32))
-        return "too many upper-level rows";
-    if (!(err = ensure_capacity(ix, ceil2(old_size + n), upper)).empty())
+        top_new = std::max(top_new, new_levels[i]);
+    }
+    if (upper >= (1ull << 32) || top_new >= rb::kMaxLevels) {
+        h.level_rng = rng_before;
+        return upper >= (1ull << 32) ? "too many upper-level rows" : "levels above 31 are not supported";
+    }
+    if (!(err = ensure_capacity(ix, ceil2(old_size + n), upper)).empty()) {
+        h.level_rng = rng_before;
         return err;
+    }
     DeviceState& d = ix->dev;
     if (device_vectors) {
         RB_CUDA(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(d.fp) + old_size * 128, device_vectors, n * 128,
@@ -962,19 +1151,12 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
     ExactPlan pl = plan_exact(rows, nq, k);
     if (workspace_bytes < pl.keys_bytes + pl.iu_bytes)
         return "workspace too small (see rb_exact_topk_workspace_bytes)";
-    static bool configured = false;
-    if (!configured) {
-        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)sizeof(rb::ExactSmem)));
-        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)rb::kTensorSmemBytes));
-        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)rb::kTensorSmemBytes));
-        RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)rb::kTensorSmemBytes));
-        configured = true;
+    {
+        std::string cerr = configure_exact_kernels();
+        if (!cerr.empty())
+            return cerr;
     }
-    rb::ExactParams ep;
+    rb::ExactParams ep{};
     ep.db = db;
     ep.queries = queries;
     ep.rows = rows;
@@ -1524,12 +1706,12 @@ void rb_load(rb_index_t* ix, char const* path, int exclude_vectors, rb_error_t* 
     std::string err = ix->host.load(path, exclude_vectors != 0);
     ix->host.ef_add = ef_add;
     ix->host.ef_search = ef_search;
+    if (!err.empty())
+        RB_FAIL(err);  // a file that does not parse leaves the index -- host and device -- as it was
     ix->device_graph_valid = false;
     ix->host_graph_valid = true;
     ix->dev.rows = 0;
     ix->dev.insert_cfg_ef = ix->dev.search_cfg_ef = 0;  // connectivity may have changed
-    if (!err.empty())
-        RB_FAIL(err);
     if (ix->dev.device >= 0 && (ix->dev.cap_rows || ix->dev.cap_upper)) {
         // row widths depend on the connectivity stored in the file: start from fresh device arrays
         int dev = ix->dev.device;
@@ -1545,10 +1727,10 @@ void rb_view(rb_index_t* ix, char const* path, int exclude_vectors, rb_error_t* 
     std::string err = ix->host.view(path, exclude_vectors != 0);
     ix->host.ef_add = ef_add;
     ix->host.ef_search = ef_search;
+    if (!err.empty())
+        RB_FAIL(err);  // a file that does not parse leaves the index as it was
     ix->device_graph_valid = false;
     ix->host_graph_valid = true;
-    if (!err.empty())
-        RB_FAIL(err);
 }
 
 void rb_metadata(char const* path, rb_metadata_t* out, rb_error_t* error) {

@@ -50,12 +50,14 @@ struct TensorSmemTail {
     uint4 thr[kTQ];
     uint32_t queue[kTEpiWarps][kTQueueCap / kTEpiWarps];  // survivors of one warp's 32 queries x 8 columns
     uint32_t queue_count[kTEpiWarps];
-    unsigned long long lkeys[kTQ][kTListK];  // per-query sorted partial lists (k <= kTListK), written back at the end
-    uint32_t liu[kTQ][kTListK];
+    // per-query sorted partial lists (k <= kTListK), written back at the end; thread = query in the epilogue, so rows
+    // are padded by one entry: the 32 lanes of a warp touching the same column hit distinct banks
+    uint32_t lnslot[kTQ][kTListK + 1];  // ~slot of each entry
+    uint32_t liu[kTQ][kTListK + 1];     // i | u << 16 of each entry: lists are ordered on the exact rationals
     uint32_t tmem_base;
     unsigned long long full[8], empty[8], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
 };
-constexpr size_t kTensorSmemBytes = kASmemBytes + kTStages * kBStageBytes + sizeof(TensorSmemTail) + 1024;
+constexpr size_t kTensorSmemBytes = kASmemBytes + kTStages * kBStageBytes + sizeof(TensorSmemTail) + 128;
 static_assert(kTStages <= 8, "barrier arrays");
 static_assert(kTensorSmemBytes <= 232448, "227 KB of shared memory per CTA");
 
@@ -181,6 +183,21 @@ __device__ __forceinline__ uint4 unpack_half_query(uint32_t w, int half) {
     return make_uint4(((w >> j) & m) << (7 - j), ((w >> (j + 1)) & m) << (6 - j), ((w >> (j + 2)) & m) << (5 - j),
                       ((w >> (j + 3)) & m) << (4 - j));
 }
+// a[c] for a run-time c without moving the array out of registers: a binary tree of 31 selects
+__device__ __forceinline__ uint32_t select32(const uint32_t (&a)[32], uint32_t c) {
+    uint32_t t16[16], t8[8], t4[4];
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+        t16[k] = (c & 16u) ? a[k + 16] : a[k];
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        t8[k] = (c & 8u) ? t16[k + 8] : t16[k];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        t4[k] = (c & 4u) ? t8[k + 4] : t8[k];
+    const uint32_t t2a = (c & 2u) ? t4[2] : t4[0], t2b = (c & 2u) ? t4[3] : t4[1];
+    return (c & 1u) ? t2b : t2a;
+}
 // padding rows carry this "popcount": >= 2048 keeps them out while a list is not full (see the filter), and small
 // enough that 128 * y * |d| stays inside 32 bits
 constexpr uint32_t kTPadRow = 4096;
@@ -240,17 +257,28 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
     unsigned char* smem_b = TS ? raw : raw + kASmemBytes;
     TensorSmemTail& s = *reinterpret_cast<TensorSmemTail*>(raw + kASmemBytes + kTStages * kBStageBytes);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t q0 = blockIdx.x * kTQ;  // may lie past the last query (the odd CTA of the last pair): all rows invalid
-    const uint32_t chunk = blockIdx.y;
+    // Triangular form (the batch tile of the build, ExactParams::tri): blockIdx.y is a LEVEL, not a chunk; the level's
+    // queries are the first tri_cnt[level] rows of the one array, query q sees rows [0, q), and the CTAs with the most
+    // rows in front of them come first in launch order.
+    const bool tri = !PAIR && !TS && p.tri != 0;
+    const uint32_t qcount = tri ? p.tri_cnt[blockIdx.y] : p.query_count;
+    const uint32_t q0 = (tri ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * kTQ;  // may lie past the last query (the odd
+                                                                                // CTA of the last pair): all rows invalid
+    if (tri && q0 >= qcount)
+        return;  // uniform: the launch is sized for the widest level
+    const uint32_t chunk = tri ? 0u : blockIdx.y;
+    const size_t out_base = tri ? (size_t)p.tri_off[blockIdx.y] : (size_t)chunk * p.query_count;  // first list of this CTA's
+                                                                                                 // level / chunk
+    const size_t bound_base = tri ? (size_t)p.tri_off[blockIdx.y] : 0;
     const uint64_t row_begin = (uint64_t)chunk * p.chunk_rows;
-    const uint64_t row_end = row_begin + p.chunk_rows < p.rows ? row_begin + p.chunk_rows : p.rows;
+    const uint64_t row_end = tri ? (qcount < q0 + kTQ - 1 ? qcount : q0 + kTQ - 1)
+                                 : (row_begin + p.chunk_rows < p.rows ? row_begin + p.chunk_rows : p.rows);
     const uint64_t n_tiles = row_begin < row_end ? (row_end - row_begin + kTD - 1) / kTD : 0;
 
     // ---- the CTA's partial lists start empty
     {
-        uint32_t nq = q0 >= p.query_count ? 0u
-                      : p.query_count - q0 < (uint32_t)kTQ ? p.query_count - q0 : (uint32_t)kTQ;
-        size_t base = ((size_t)chunk * p.query_count + q0) * p.k;
+        uint32_t nq = q0 >= qcount ? 0u : qcount - q0 < (uint32_t)kTQ ? qcount - q0 : (uint32_t)kTQ;
+        size_t base = (out_base + q0) * p.k;
         for (size_t i = tid; i < (size_t)nq * p.k; i += kTThreads)
             p.partial_keys[base + i] = ~0ull;
     }
@@ -260,12 +288,10 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
     // ---- query tile: popcounts, thresholds, and the resident unpacked A operand
     for (int r = tid; r < kTQ; r += kTThreads) {
         uint32_t q = q0 + r, pc = 0;
-        if (q < p.query_count)
+        if (q < qcount)
             for (int w = 0; w < 8; ++w)
                 pc += popc4(__ldg(p.queries + (size_t)q * 8 + w));
-        s.pq[r] = q < p.query_count ? pc : kXInvalid;
-        for (int j = 0; j < kTListK; ++j)
-            s.lkeys[r][j] = ~0ull;
+        s.pq[r] = q < qcount ? pc : kXInvalid;
         s.thr[r] = make_uint4(0, 1, 0, 2048);  // list not full: every valid row (|d| < 2048) passes, padding rows do not
     }
     if (!TS) {
@@ -273,7 +299,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         for (int idx = tid; idx < kTQ * 64; idx += kTThreads) {
             int r = idx & (kTQ - 1), k16 = idx >> 7;
             uint32_t q = q0 + r;
-            uint32_t w = q < p.query_count ? __ldg(q32 + (size_t)q * 32 + (k16 >> 1)) : 0u;
+            uint32_t w = q < qcount ? __ldg(q32 + (size_t)q * 32 + (k16 >> 1)) : 0u;
             *reinterpret_cast<uint4*>(smem_a + (r >> 3) * kSBO_A + k16 * kLBO + (r & 7) * 16) =
                 unpack_half_query(w, k16 & 1);
         }
@@ -321,7 +347,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
             const uint4* qrow = p.queries + (size_t)q * 8;
 #pragma unroll 1
             for (int c = 0; c < 8; ++c) {
-                const uint4 v = q < p.query_count ? __ldg(qrow + c) : make_uint4(0, 0, 0, 0);
+                const uint4 v = q < qcount ? __ldg(qrow + c) : make_uint4(0, 0, 0, 0);
                 const uint32_t w[4] = {v.x, v.y, v.z, v.w};
                 uint32_t r[32];
 #pragma unroll
@@ -509,6 +535,11 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         const uint32_t pqv = s.pq[ql];
         const bool smem_lists = p.k <= (uint32_t)kTListK;
         const bool share_bounds = smem_lists && p.bounds != nullptr;  // bound word: d bits << 32 | chunk << 23 | i << 12 | u
+        // this thread's own list (k <= kTListK): length, and its worst entry once it is full -- counts, ~slot, and the
+        // reference-exact distance bits that bound words are compared on
+        const uint32_t kk = p.k;
+        uint32_t llen = 0, w_i = 0, w_u = 1, w_ns = 0, w_pos = 0, own_bits = 0xFFFFFFFFu;
+        unsigned long long n_hits = 0, n_ins = 0;  // RB_EXACT_DEBUG / RB_TILE_DEBUG: filter survivors and list insertions
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;
             const int a = (int)(t & 1);            // popcount side array of this tile
@@ -531,9 +562,9 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
             // a row of a higher chunk wins the tie on its slot (non-strict, w = 1).  Which survivors take the slow path
             // depends on timing; the result does not.
             if (share_bounds && pqv != kXInvalid) {
-                const unsigned long long g = __ldcg(p.bounds + q0 + ql);
-                const unsigned long long own = s.lkeys[ql][p.k - 1];
-                if (g != ~0ull && (own == ~0ull || (uint32_t)(g >> 32) < (uint32_t)(own >> 32))) {
+                const unsigned long long g = __ldcg(p.bounds + bound_base + q0 + ql);
+                if (g != ~0ull && (llen < kk || (!tri && (uint32_t)(g >> 32) < own_bits))) {  // (a triangular list,
+                    // once full, is tighter than its seed: every entry passed it)
                     const uint32_t holder = (uint32_t)(g >> 23) & 0x1FFu;
                     const uint32_t it_ = (uint32_t)(g >> 12) & 0x7FFu, ut = (uint32_t)g & 0xFFFu;
                     s.thr[ql] = make_uint4(ut + it_, it_, it_ * pqv, chunk < holder ? 0u : 1u);
@@ -586,21 +617,102 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                 const uint32_t any_hit = pqv == kXInvalid ? 0u : (hm[0] | hm[1] | hm[2] | hm[3]);
                 long long te2 = dbg ? clock64() : 0, te3 = te2;
                 uint32_t qn_total = 0;
+                if (smem_lists) {
+                    // Survivors, lists in shared memory (k <= kTListK): thread = query, so every thread works through
+                    // ITS OWN survivors while the other lanes do the same for theirs.  Entries are compared on the exact
+                    // rationals (i1 u2 > i2 u1: closer; equal ratios: the higher slot first -- the order of the keys
+                    // distance bits << 32 | ~slot without forming them).  The list is UNSORTED with its worst entry
+                    // tracked in registers: a survivor costs two multiplies against the worst entry and, when it
+                    // enters, overwrites it and rescans the k entries for the new worst (independent loads; a sorted
+                    // insert is a chain of dependent shared-memory round trips, measured ~1.7 k cycles per survivor).
+                    // The list is sorted, and the f64 divide of the reference-exact bits paid, once, when it is
+                    // published.  The final list is the top-k of all survivors under a total order.
+                    // (The survivor code is kept SMALL and rolled: it runs a few times per tile from a cold instruction
+                    // cache, and the four-fold unrolled version of it -- 2800 instructions -- cost ~1.7 k cycles per
+                    // survivor whatever the list algorithm was.)
+                    if (any_hit) {
+                        // bit 8 r + 7 - j of `hits` <-> column 8 r + j of the block
+                        uint32_t hits = (hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0];
+                        n_hits += __popc(hits);
+                        uint32_t* ls = &s.lnslot[ql][0];
+                        uint32_t* li = &s.liu[ql][0];
+                        bool changed = false;
+#pragma unroll 1
+                        while (hits) {
+                            const uint32_t bit = 31u - (uint32_t)__clz((int)hits);
+                            hits &= ~(1u << bit);
+                            const uint32_t col = (bit & 24u) | (7u - (bit & 7u));
+                            const uint32_t iv = select32(acc, col) >> kTScaleLog2;
+                            const uint32_t dl = (uint32_t)(b * 32) + col;
+                            const uint32_t pdv = s.pd[a][dl];
+                            if (pdv >= kTPadRow)  // a padding row can pass a non-strict bound with i_t = 0
+                                continue;
+                            const uint64_t row = row_begin + tile * kTD + dl;
+                            if (tri && row >= (uint64_t)q0 + (uint32_t)ql)
+                                continue;         // triangular form: only the rows in front of the query
+                            const uint32_t u = pqv + pdv - iv, uu = u ? u : 1u;  // u == 0: distance 1 = ratio 0
+                            const uint32_t ns = ~(uint32_t)(p.slot_base + row);
+                            if (llen == kk) {
+                                const uint32_t lhs = iv * w_u, rhs = w_i * uu;  // counts <= 1024, unions <= 2048
+                                if (lhs < rhs || (lhs == rhs && ns > w_ns))
+                                    continue;
+                                // replace the worst entry, then find the new worst: independent loads, no chain
+                                li[w_pos] = iv | (uu << 16);
+                                ls[w_pos] = ns;
+                                uint32_t ci = iv, cu = uu, cns = ns, cpos = w_pos;
+#pragma unroll 1
+                                for (uint32_t e0 = 0; e0 < kk; e0 += 4) {  // four entries per round: their loads overlap
+                                    uint32_t eiu[4], ens[4];
+#pragma unroll
+                                    for (uint32_t t4 = 0; t4 < 4; ++t4) {  // (rows hold kTListK + 1 >= e0 + 4 entries)
+                                        eiu[t4] = li[e0 + t4];
+                                        ens[t4] = ls[e0 + t4];
+                                    }
+#pragma unroll
+                                    for (uint32_t t4 = 0; t4 < 4; ++t4) {
+                                        const uint32_t l2 = (eiu[t4] & 0xFFFFu) * cu, r2 = ci * (eiu[t4] >> 16);
+                                        // entry e0 + t4 is farther than the candidate
+                                        if (e0 + t4 < kk && (l2 < r2 || (l2 == r2 && ens[t4] > cns)))
+                                            ci = eiu[t4] & 0xFFFFu, cu = eiu[t4] >> 16, cns = ens[t4], cpos = e0 + t4;
+                                    }
+                                }
+                                w_i = ci, w_u = cu, w_ns = cns, w_pos = cpos;
+                            } else {
+                                li[llen] = iv | (uu << 16);
+                                ls[llen] = ns;
+                                // the worst of a list that is not full yet only matters when it becomes full
+                                if (llen == 0 || iv * w_u < w_i * uu || (iv * w_u == w_i * uu && ns > w_ns))
+                                    w_i = iv, w_u = uu, w_ns = ns, w_pos = llen;
+                                ++llen;
+                            }
+                            changed = true;
+                            ++qn_total;
+                            ++n_ins;
+                        }
+                        if (changed && llen == kk) {
+                            s.thr[ql] = make_uint4(w_u + w_i, w_i, w_i * pqv, 0);
+                            if (share_bounds && !tri) {  // (triangular form: one CTA per query, nobody to share with)
+                                own_bits = exact_distance_bits(w_i, w_u);
+                                atomicMin(p.bounds + bound_base + q0 + ql,
+                                          ((unsigned long long)own_bits << 32) | ((unsigned long long)chunk << 23) |
+                                              ((unsigned long long)w_i << 12) | w_u);
+                            }
+                        }
+                    }
+                } else
                 if (__any_sync(RB_FULL_MASK, any_hit != 0)) {
                     // rare: rounds of 8 columns from the HIGHEST rows down (round r = columns 8 r .. 8 r + 7); a survivor
                     // always belongs to one of this warp's own 32 queries, so the slow path is warp-local
-#pragma unroll
+                    const uint32_t hits = pqv == kXInvalid ? 0u : ((hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0]);
+#pragma unroll 1
                     for (int r = 3; r >= 0; --r) {
-                        uint32_t hit = pqv == kXInvalid ? 0u : hm[r];
+                        uint32_t hit = (hits >> (8 * r)) & 0xFFu;
                         if (!__any_sync(RB_FULL_MASK, hit != 0))
                             continue;
                         while (hit) {
                             const int j = 7 - (31 - __clz((int)hit));  // bit 7 - j <-> column 8 r + j
                             hit &= ~(0x80u >> j);
-                            uint32_t iv = 0;
-#pragma unroll
-                            for (int e = 0; e < 8; ++e)  // acc[] lives in registers: select without dynamic indexing
-                                iv = (e == j) ? (acc[r * 8 + e] >> kTScaleLog2) : iv;
+                            const uint32_t iv = select32(acc, (uint32_t)(r * 8 + j)) >> kTScaleLog2;
                             uint32_t at = atomicAdd(&s.queue_count[warp], 1u);
                             s.queue[warp][at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + r * 8 + j) << 16) | iv;
                         }
@@ -614,30 +726,20 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                                 uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
                                 if (s.pd[a][dl] >= kTPadRow)  // a padding row can pass a non-strict bound with i_t = 0
                                     continue;                 // (warp-uniform: every lane looks at the same entry)
+                                if (tri && row_begin + tile * kTD + dl >= (uint64_t)q0 + eq)
+                                    continue;                 // triangular form: only the rows in front of the query
                                 uint32_t u = s.pq[eq] + s.pd[a][dl] - i;
                                 uint32_t slot = (uint32_t)(p.slot_base + row_begin + tile * kTD + dl);
                                 uint64_t key = ((uint64_t)exact_distance_bits(i, u) << 32) | (uint32_t)~slot;
-                                uint64_t* lk;
-                                uint32_t* li;
-                                if (smem_lists) {
-                                    lk = reinterpret_cast<uint64_t*>(&s.lkeys[eq][0]);
-                                    li = &s.liu[eq][0];
-                                } else {
-                                    size_t off = ((size_t)chunk * p.query_count + q0 + eq) * p.k;
-                                    lk = p.partial_keys + off;
-                                    li = p.partial_iu + off;
-                                }
+                                const size_t off = (out_base + q0 + eq) * p.k;  // k > kTListK: lists in global memory
+                                uint64_t* lk = p.partial_keys + off;
+                                uint32_t* li = p.partial_iu + off;
                                 glist_insert(lk, li, p.k, key, i | ((u ? u : 1u) << 16));
                                 if (lk[p.k - 1] != ~0ull) {
                                     uint32_t iu = li[p.k - 1];
                                     uint32_t it_ = iu & 0xFFFFu, ut = iu >> 16;
-                                    if (lane == 0) {
+                                    if (lane == 0)
                                         s.thr[eq] = make_uint4(ut + it_, it_, it_ * s.pq[eq], 0);
-                                        if (share_bounds)
-                                            atomicMin(p.bounds + q0 + eq,
-                                                      ((lk[p.k - 1] >> 32) << 32) | ((unsigned long long)chunk << 23) |
-                                                          ((unsigned long long)it_ << 12) | ut);
-                                    }
                                 }
                                 __syncwarp();
                             }
@@ -665,10 +767,34 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                 }
             }
         }
-        if (smem_lists && pqv != kXInvalid) {  // publish this query's partial list
-            size_t off = ((size_t)chunk * p.query_count + q0 + ql) * p.k;
-            for (uint32_t j = 0; j < p.k; ++j)
-                p.partial_keys[off + j] = s.lkeys[ql][j];
+        if (p.debug_cycles != nullptr && blockIdx.x == 0 && blockIdx.y == 0) {
+            atomicAdd(p.debug_cycles + 29, n_hits);
+            atomicAdd(p.debug_cycles + 30, n_ins);
+        }
+        if (smem_lists && pqv != kXInvalid) {  // publish this query's partial list: sorted, reference-exact bits at last
+            size_t off = (out_base + q0 + ql) * p.k;
+            uint32_t* ls = &s.lnslot[ql][0];
+            uint32_t* li = &s.liu[ql][0];
+            for (uint32_t j = 1; j < llen; ++j) {  // insertion sort, closest first
+                const uint32_t eiu = li[j], ens = ls[j];
+                uint32_t pos = j;
+                while (pos > 0) {
+                    const uint32_t piu = li[pos - 1], pns = ls[pos - 1];
+                    const uint32_t lhs = (eiu & 0xFFFFu) * (piu >> 16), rhs = (piu & 0xFFFFu) * (eiu >> 16);
+                    if (!(lhs > rhs || (lhs == rhs && ens < pns)))
+                        break;
+                    li[pos] = piu;
+                    ls[pos] = pns;
+                    --pos;
+                }
+                li[pos] = eiu;
+                ls[pos] = ens;
+            }
+            for (uint32_t j = 0; j < kk; ++j) {
+                const uint32_t eiu = li[j];
+                p.partial_keys[off + j] =
+                    j < llen ? (((unsigned long long)exact_distance_bits(eiu & 0xFFFFu, eiu >> 16) << 32) | ls[j]) : ~0ull;
+            }
         }
     }
     if (dbg && (warp == kTProdWarp0 || warp == kTMmaWarp || warp == 0)) {

@@ -39,6 +39,13 @@ struct ExactParams {
     unsigned long long* bounds;        // [Q], ~0 at launch (tensor-core kernels): the smallest k-th-best key any CTA has
                                        // reached for the query so far, distance bits << 32 | i << 16 | u
     unsigned long long* debug_cycles;  // optional [32] cycle counters of the tensor kernel's roles (profiling aid)
+    // TRIANGULAR form (the batch tile of the build, exact_topk_i8_kernel_t<0> only): queries == db == one array in
+    // work order; grid.y = level; level l covers the first tri_cnt[l] rows, a query only sees the rows IN FRONT of it,
+    // its list and bound word live at entry tri_off[l] + query of partial_keys / bounds (one "chunk"), and the bound
+    // words arrive SEEDED (insert_search_kernel) instead of ~0.
+    uint32_t tri;
+    uint32_t tri_cnt[32];
+    uint32_t tri_off[32];
 };
 
 struct ExactSmem {

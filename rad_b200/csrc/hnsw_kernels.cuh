@@ -613,6 +613,22 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
 }
 
 // ------------------------------------------------------------------------------------------------ insertion
+// A batch is inserted in three steps (the executable specification is tests/model/batched_model.c):
+//   insert_search_kernel   every node's greedy descent and ef-bounded searches against the FROZEN graph of the nodes
+//                          before the batch; the sorted candidate list of every (node, level) task is kept in global
+//                          memory, and the entry at rank min(ef, kSeedRank) becomes the SEED bound of the batch tile
+//   batch tile             exact_topk_i8_kernel_t<0> in its triangular form (exact_i8_kernels.cuh): the nodes of a batch
+//                          never meet in the frozen graph, so every task is offered its kBatchMates nearest EARLIER
+//                          batch-mates (work order: more levels first, then ascending slot), exact, on the tensor cores
+//   insert_select_kernel   batch-mates merged into the list, the reference's heuristic (index.hpp:4246-4289), forward
+//                          links, link popcounts and the reverse-link records
+constexpr int kBatchMates = 16;
+// A batch-mate is offered to a task only if it is strictly closer than the task's candidate at this rank (or at rank ef
+// when ef is smaller): the heuristic keeps M <= 16 links from the front of the list, and what lies behind rank 128
+// does not change the graph's recall (tests/model, scripts/model_recall_probe.py) but triples the tile's survivors.
+constexpr int kSeedRank = 128;
+constexpr int kMaxLevels = 32;  // levels 0 .. 31 (P(level >= 32) = M^-32 per node)
+
 struct InsertParams {
     GraphView g;
     const int8_t* levels;      // per slot
@@ -627,12 +643,20 @@ struct InsertParams {
     unsigned int* work_counter;
     unsigned long long* counters;  // [0] distances, [1] expansions
     const uint32_t* order;         // the t-th unit of work of the batch is node batch_start + order[t]
+    // per-(level, position) arrays, level-major: entry level_off[level] + t belongs to the node at position t
+    uint64_t* lists;               // [tasks x ef]   sorted candidate keys of the task
+    uint32_t* lens;                // [tasks]
+    unsigned long long* seeds;     // [tasks]        bound word of the batch tile (exact_i8_kernels.cuh), ~0 = none
+    const uint64_t* mate_keys;     // [tasks x kBatchMates]  tile output: distance bits << 32 | ~position, ~0 padding
+    uint4* batch_fp;               // [batch_size x 8]  the batch's fingerprints in work order (the tile's operand)
+    uint32_t level_off[kMaxLevels];
+    uint32_t use_mates;            // 0: no batch tile ran (select uses the lists alone)
 };
 
 // MINB = resident CTAs per SM the register budget is sized for: 4 (<= 128 registers, 8 loads in flight per lane) when
 // shared memory allows no more, 6 or 8 when the per-warp scratch is small enough to fit them
 template <int MINB>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_kernel(InsertParams p) {
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_search_kernel(InsertParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
     WarpScratch w = carve_scratch(smem + (size_t)warp * warp_scratch_bytes(p.ef, p.bloom_log2, p.g.m), p.ef,
@@ -647,14 +671,97 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_kernel(Inser
             break;
         const uint32_t slot = p.batch_start + __ldg(p.order + t);
         const uint4 q4 = load_slice(p.g.fp, slot, sub);
+        if (lane < 8)
+            p.batch_fp[(size_t)t * 8 + sub] = q4;
         const int lq = p.levels[slot];
         uint32_t cur = p.entry;
         uint32_t cur_bits = warp_eval_one(p.g.fp, q4, cur);
         tc.distances += 1;
         warp_greedy_descent(p.g, q4, cur, cur_bits, p.max_level, lq, tc);
+        for (int level = lq < p.max_level ? lq : p.max_level; level >= 0; --level) {
+            const uint32_t len = warp_beam_search(p.g, w, q4, cur, cur_bits, level, p.ef, tc);
+            const size_t idx = (size_t)p.level_off[level] + t;
+            uint64_t* out = p.lists + idx * p.ef;
+            for (uint32_t i = lane; i < len; i += 32)
+                out[i] = w.list[i];
+            // seed of the batch tile: the exact counts of the list entry at rank min(ef, kSeedRank)
+            unsigned long long seed = ~0ull;
+            const uint32_t seed_rank = p.ef < (uint32_t)kSeedRank ? p.ef : (uint32_t)kSeedRank;
+            if (len >= seed_rank) {
+                const uint32_t v = group8_inter_union(load_slice(p.g.fp, key_slot(w.list[seed_rank - 1]), sub), q4);
+                const uint32_t i_t = v & 0xFFFFu, u_t = v >> 16;
+                seed = ((unsigned long long)exact_distance_bits(i_t, u_t) << 32) | (0x1FFull << 23) |
+                       ((unsigned long long)i_t << 12) | u_t;
+            }
+            if (lane == 0) {
+                p.lens[idx] = len;
+                p.seeds[idx] = seed;
+            }
+            const uint64_t k0 = w.list[0];
+            cur = key_slot(k0);
+            cur_bits = key_bits(k0);
+            __syncwarp();
+        }
+    }
+    if (lane == 0) {
+        atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+        atomicAdd(p.counters + 1, (unsigned long long)tc.expansions);
+    }
+}
+
+// per-warp scratch of insert_select_kernel: the list, the kept fingerprints of the heuristic and its selection
+__host__ __device__ inline size_t select_scratch_bytes(uint32_t ef, uint32_t kept_rows) {
+    return (((size_t)ef * 8 + 15) & ~(size_t)15) + (size_t)kept_rows * 128 + kMaxWidth * 8;
+}
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) insert_select_kernel(InsertParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7;
+    WarpScratch w;
+    {
+        unsigned char* base = smem + (size_t)warp * select_scratch_bytes(p.ef, p.g.m);
+        w.list = reinterpret_cast<uint64_t*>(base);
+        base += ((size_t)p.ef * 8 + 15) & ~(size_t)15;
+        w.kept = reinterpret_cast<uint4*>(base);
+        w.sel = reinterpret_cast<uint64_t*>(base + (size_t)p.g.m * 128);
+        w.bloom = nullptr;
+        w.pend = nullptr;
+        w.ids = nullptr;
+        w.bloom_log2 = 0;
+    }
+    TraversalCounters tc{0, 0};
+    for (;;) {
+        uint32_t t = 0;
+        if (lane == 0)
+            t = atomicAdd(p.work_counter, 1u);
+        t = __shfl_sync(RB_FULL_MASK, t, 0);
+        if (t >= p.batch_size)
+            break;
+        const uint32_t slot = p.batch_start + __ldg(p.order + t);
+        const uint4 q4 = load_slice(p.g.fp, slot, sub);
+        const int lq = p.levels[slot];
         uint32_t task = p.task_rel[slot];
         for (int level = lq < p.max_level ? lq : p.max_level; level >= 0; --level, ++task) {
-            uint32_t len = warp_beam_search(p.g, w, q4, cur, cur_bits, level, p.ef, tc);
+            const size_t idx = (size_t)p.level_off[level] + t;
+            uint32_t len = p.lens[idx];
+            {
+                const uint64_t* in = p.lists + idx * p.ef;
+                for (uint32_t i = lane; i < len; i += 32)
+                    w.list[i] = in[i];
+            }
+            __syncwarp();
+            if (p.use_mates) {
+                // the tile's answers are positions in the batch's work order, ascending by (distance, -position)
+                const uint64_t mk = lane < kBatchMates ? p.mate_keys[idx * kBatchMates + lane] : ~0ull;
+                const uint32_t cnt = __popc(__ballot_sync(RB_FULL_MASK, mk != ~0ull));  // a prefix of the lanes
+                if (cnt) {
+                    const uint32_t mslot =
+                        (uint32_t)lane < cnt ? p.batch_start + __ldg(p.order + (~(uint32_t)mk)) : 0u;
+                    const uint32_t bits = warp_eval(p.g.fp, q4, mslot, cnt);
+                    tc.distances += cnt;
+                    list_merge(w.list, len, p.ef, make_key(bits, mslot), (uint32_t)lane < cnt);
+                }
+            }
             uint32_t ns = warp_select_neighbors(p.g, w, w.list, len, p.g.m, tc, q4);
             uint32_t width;
             uint32_t* mine = graph_row(p.g, slot, level, width);
@@ -670,16 +777,11 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_kernel(Inser
                 p.pair_keys[at] = on ? (((uint64_t)(uint32_t)level << 32) | key_slot(sk)) : ~0ull;
                 p.pair_vals[at] = on ? (((uint64_t)key_bits(sk) << 32) | slot) : 0ull;
             }
-            uint64_t k0 = w.list[0];
-            cur = key_slot(k0);
-            cur_bits = key_bits(k0);
             __syncwarp();
         }
     }
-    if (lane == 0) {
+    if (lane == 0)
         atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
-        atomicAdd(p.counters + 1, (unsigned long long)tc.expansions);
-    }
 }
 
 // ------------------------------------------------------------------------------------------------ reverse links
@@ -880,6 +982,32 @@ __global__ void __launch_bounds__(256) link_popcount_kernel(const uint32_t* __re
         const uint32_t id = __ldg(adj + i);
         out[i] = id == RB_EMPTY ? (uint16_t)0 : __ldg(node_pc + id);
     }
+}
+
+// ------------------------------------------------------------------------------------------------ level statistics
+// Edges per level of the whole graph (index.hpp:3147-3179 counts them by walking every node on the host): counted here,
+// where the adjacency was produced, and handed to the host with it at rb_sync_host.  One thread per node.
+__global__ void __launch_bounds__(256) edge_count_kernel(GraphView g, const int8_t* __restrict__ levels, uint32_t rows,
+                                                         unsigned long long* __restrict__ out /* [kMaxLevels] */) {
+    __shared__ unsigned int local[kMaxLevels];
+    if (threadIdx.x < kMaxLevels)
+        local[threadIdx.x] = 0;
+    __syncthreads();
+    for (uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x; slot < rows; slot += gridDim.x * blockDim.x) {
+        const int lv = levels[slot];
+        for (int level = 0; level <= lv && level < kMaxLevels; ++level) {
+            uint32_t width;
+            const uint32_t* row = graph_row(g, slot, level, width);
+            uint32_t cnt = 0;
+            for (uint32_t j = 0; j < width; ++j)
+                cnt += row[j] != RB_EMPTY;
+            if (cnt)
+                atomicAdd(&local[level], cnt);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < kMaxLevels && local[threadIdx.x])
+        atomicAdd(out + threadIdx.x, (unsigned long long)local[threadIdx.x]);
 }
 
 // ------------------------------------------------------------------------------------------------ approximate search

@@ -187,7 +187,9 @@ void HostIndex::reset_graph() {
     map_valid_ = false;
     keys_ascending_ = true;
     max_key_ = 0;
-    stats_cache_size_ = (size_t)-1;
+    level_nodes_.clear();
+    top_nodes_.clear();
+    edges_valid_ = false;
     vectors_excluded = false;
 }
 
@@ -245,49 +247,110 @@ int HostIndex::neighbors(size_t slot, int level, uint32_t* out, size_t cap) cons
     return (int)cnt;
 }
 
-void HostIndex::ensure_stats() const {
-    size_t n = size();
-    if (stats_cache_size_ == n)
-        return;
-    int top = 0;
-    for (size_t i = 0; i < n; ++i)
-        top = std::max(top, level_of(i));
-    std::vector<LevelStats> st((size_t)top + 1);
-    top_cache_.clear();
-    uint32_t tmp[64];
-    for (size_t i = 0; i < n; ++i) {
-        int l = level_of(i);
-        for (int lv = 0; lv <= l; ++lv) {
-            int cnt = neighbors(i, lv, tmp, 64);
-            st[lv].nodes++;
-            st[lv].edges += (uint64_t)std::max(cnt, 0);
-            st[lv].allocated_bytes += lv ? 4 * (1 + (size_t)m) : 10 + 4 * (1 + (size_t)m0);
+void HostIndex::note_new_levels(size_t first_slot, int16_t const* new_levels, size_t count) {
+    for (size_t i = 0; i < count; ++i) {
+        const int l = new_levels[i];
+        if ((size_t)l + 1 > level_nodes_.size())
+            level_nodes_.resize((size_t)l + 1, 0);
+        for (int lv = 0; lv <= l; ++lv)
+            ++level_nodes_[lv];
+        // the top level of the graph is the highest level seen so far (index.hpp:2761-2781: a node above it becomes
+        // the entry point); nodes AT that level are what get_top_level_nodes returns
+        const int top = (int)level_nodes_.size() - 1;
+        if (l == top) {
+            if (level_nodes_[top] == 1)
+                top_nodes_.clear();
+            top_nodes_.push_back((uint32_t)(first_slot + i));
         }
-        if (n && l == max_level)
-            top_cache_.push_back((uint32_t)i);
     }
-    for (size_t lv = 0; lv < st.size(); ++lv)
-        st[lv].max_edges = st[lv].nodes * (lv ? m : m0);
-    stats_cache_.swap(st);
-    stats_cache_size_ = n;
+}
+
+void HostIndex::rebuild_level_index() {
+    level_nodes_.clear();
+    top_nodes_.clear();
+    const size_t n = size();
+    // one sequential pass over the level array (2 bytes per node), in blocks so that the histogram stays in registers
+    uint64_t hist[64] = {0};
+    int top = 0;
+    for (size_t i = 0; i < n; ++i) {
+        const int l = level_of(i);
+        ++hist[std::min(l, 63)];
+        top = std::max(top, l);
+    }
+    if (n) {
+        level_nodes_.assign((size_t)top + 1, 0);
+        uint64_t acc = 0;
+        for (int l = std::min(top, 63); l >= 0; --l) {
+            acc += hist[l];
+            level_nodes_[l] = acc;
+        }
+        for (size_t i = 0; i < n; ++i)
+            if (level_of(i) == top)
+                top_nodes_.push_back((uint32_t)i);
+    }
+    std::lock_guard<std::mutex> lock(mu_);
+    edges_valid_ = false;
+}
+
+void HostIndex::set_level_edges(std::vector<uint64_t> const& edges) {
+    std::lock_guard<std::mutex> lock(mu_);
+    level_edges_ = edges;
+    level_edges_.resize(std::max(level_edges_.size(), level_nodes_.size()), 0);
+    edges_valid_ = true;
+}
+
+void HostIndex::invalidate_level_edges() {
+    std::lock_guard<std::mutex> lock(mu_);
+    edges_valid_ = false;
+}
+
+// edges per level of a loaded / viewed graph: one pass over the lists, split over host threads, once
+void HostIndex::ensure_edges() const {
+    std::lock_guard<std::mutex> lock(mu_);
+    if (edges_valid_)
+        return;
+    const size_t n = size(), nl = level_nodes_.size();
+    const size_t threads = std::min<size_t>({16, std::max(1u, std::thread::hardware_concurrency()), n / 65536 + 1});
+    std::vector<std::vector<uint64_t>> part(threads, std::vector<uint64_t>(nl, 0));
+    auto work = [&](size_t t) {
+        uint32_t tmp[64];
+        const size_t lo = n * t / threads, hi = n * (t + 1) / threads;
+        for (size_t i = lo; i < hi; ++i) {
+            const int l = level_of(i);
+            for (int lv = 0; lv <= l && (size_t)lv < nl; ++lv)
+                part[t][lv] += (uint64_t)std::max(neighbors(i, lv, tmp, 64), 0);
+        }
+    };
+    if (threads <= 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> pool;
+        for (size_t t = 0; t < threads; ++t)
+            pool.emplace_back(work, t);
+        for (std::thread& th : pool)
+            th.join();
+    }
+    level_edges_.assign(nl, 0);
+    for (size_t t = 0; t < threads; ++t)
+        for (size_t lv = 0; lv < nl; ++lv)
+            level_edges_[lv] += part[t][lv];
+    edges_valid_ = true;
 }
 
 bool HostIndex::level_stats(size_t level, LevelStats& out) const {
-    ensure_stats();
-    if (level >= stats_cache_.size()) {
-        if (level <= (size_t)max_level || level == 0) {
-            out = LevelStats{};
-            return true;
-        }
-        return false;
-    }
-    out = stats_cache_[level];
+    out = LevelStats{};
+    if (level >= level_nodes_.size())
+        return level <= (size_t)max_level || level == 0;
+    ensure_edges();
+    out.nodes = level_nodes_[level];
+    out.edges = level_edges_[level];
+    out.max_edges = out.nodes * (level ? m : m0);
+    out.allocated_bytes = out.nodes * (level ? 4 * (1 + (size_t)m) : 10 + 4 * (1 + (size_t)m0));
     return true;
 }
 
 size_t HostIndex::top_level_nodes(std::vector<uint32_t>& out) const {
-    ensure_stats();
-    out = top_cache_;
+    out = top_nodes_;
     return out.size();
 }
 
@@ -323,6 +386,7 @@ void HostIndex::rebuild_keymap() {
 }
 
 int64_t HostIndex::slot_of_key(uint64_t key) {
+    std::lock_guard<std::mutex> lock(mu_);  // the map is built on first use; concurrent readers must not race on it
     if (!map_valid_)
         rebuild_keymap();
     return map_keys_.find(key);
@@ -379,7 +443,7 @@ void HostIndex::truncate_rows(size_t rows, int32_t old_max_level, uint64_t old_e
             keys_ascending_ = false;
         max_key_ = std::max(max_key_, keys[i]);
     }
-    stats_cache_size_ = (size_t)-1;
+    rebuild_level_index();
 }
 
 // ------------------------------------------------------------------------------------------------ file format
@@ -654,7 +718,7 @@ std::string HostIndex::view(char const* path, bool exclude_vectors) {
     vectors_excluded = exclude_vectors || !md.has_vectors;
     view_vectors_ = vectors_excluded ? nullptr : data + (md.head_offset - md.matrix_rows * md.matrix_cols);
     map_valid_ = false;
-    stats_cache_size_ = (size_t)-1;
+    rebuild_level_index();
     return {};
 }
 
@@ -703,6 +767,7 @@ std::string HostIndex::load(char const* path, bool exclude_vectors) {
             keys_ascending_ = false;
         max_key_ = std::max(max_key_, keys[i]);
     }
+    rebuild_level_index();
     return {};
 }
 

@@ -16,6 +16,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -101,6 +102,11 @@ class HostIndex {
     void note_new_keys(uint64_t const* new_keys, size_t n);
     // undo an append that was committed before the device confirmed it: keep the first `rows` nodes
     void truncate_rows(size_t rows, int32_t old_max_level, uint64_t old_entry);
+    // per-level population (kept from the levels alone, see below): call after `levels` grew by `count` rows
+    void note_new_levels(size_t first_slot, int16_t const* new_levels, size_t count);
+    // edges per level counted where the adjacency was produced (the device, at rb_sync_host): no host scan needed
+    void set_level_edges(std::vector<uint64_t> const& edges);
+    void invalidate_level_edges();
 
     // serialisation; `vectors` may be null only when exclude_vectors
     std::string save(char const* path, uint8_t const* vectors, bool exclude_vectors) const;
@@ -129,11 +135,19 @@ class HostIndex {
     bool keys_ascending_ = true;  // keys were added in strictly ascending order so far
     uint64_t max_key_ = 0;
 
-    // per-level statistics cache
-    mutable std::vector<LevelStats> stats_cache_;
-    mutable size_t stats_cache_size_ = (size_t)-1;
-    mutable std::vector<uint32_t> top_cache_;
-    void ensure_stats() const;
+    // Per-level metadata.  The reference rescans every node for get_top_level_nodes (python/lib.cpp:290-305) and every
+    // node AND list for stats (index.hpp:3147-3179) on each call.  Here the node counts per level and the list of
+    // top-level nodes are maintained from the LEVELS alone, as they arrive (add / load / view) -- they never touch the
+    // adjacency, so they are valid even while the host copy of a freshly built graph is stale.  Edge counts come with
+    // the adjacency: from the device at rb_sync_host, or from one parallel pass over a loaded / viewed tape on first
+    // use.  A mutex guards the lazily built parts (RAD's threaded hnsw_server calls these concurrently).
+    std::vector<uint64_t> level_nodes_;  // [l] = nodes with level >= l
+    std::vector<uint32_t> top_nodes_;    // slots of the nodes at max level, ascending
+    mutable std::vector<uint64_t> level_edges_;
+    mutable bool edges_valid_ = false;
+    mutable std::mutex mu_;
+    void rebuild_level_index();
+    void ensure_edges() const;
 };
 
 }  // namespace rbh

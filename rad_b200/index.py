@@ -198,6 +198,7 @@ class Index:
         batch_max: int = 0,
         bloom_bits_log2: int = 0,
         _debug_max_batches: int = 0,
+        _no_batch_tile: bool = False,
     ) -> None:
         if connectivity is None:
             connectivity = DEFAULT_CONNECTIVITY
@@ -222,7 +223,7 @@ class Index:
             flags=(_native.RB_FLAG_LAZY_HOST_SYNC if lazy_host_sync else 0)
             | (_native.RB_FLAG_TIME_KERNELS if time_kernels else 0),
             batch_growth_den=batch_growth_den, batch_max=batch_max, bloom_bits_log2=bloom_bits_log2,
-            debug_max_batches=_debug_max_batches)
+            debug_max_batches=_debug_max_batches, no_batch_tile=1 if _no_batch_tile else 0)
         err = C.c_char_p()
         self._lib = _native.lib()
         self._h = self._lib.rb_init(C.byref(opts), C.byref(err))
@@ -562,7 +563,8 @@ class Index:
         return dict(computed_distances=int(c.computed_distances), visited_members=int(c.visited_members),
                     batches=int(c.batches), kernel_launches=int(c.kernel_launches), device_ms=float(c.device_ms),
                     insert_ms=float(c.insert_ms), sort_ms=float(c.sort_ms), reverse_ms=float(c.reverse_ms),
-                    insert_launches=int(c.insert_launches))
+                    insert_launches=int(c.insert_launches), tile_ms=float(c.tile_ms),
+                    select_ms=float(c.select_ms))
 
     def sync_host(self) -> None:
         err = C.c_char_p()

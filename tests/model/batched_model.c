@@ -32,6 +32,7 @@
 #define EMPTY 0xFFFFFFFFu
 #define CAND_MAX 64
 #define INCOMING_CAP 256
+#define SEED_RANK 128u
 
 typedef struct {
     uint32_t m, m0, ef;
@@ -429,8 +430,8 @@ BM_EXPORT void bm_build(bm_index* ix, uint64_t upto, uint64_t max_batches) {
          * batch: nodes with more levels to search first, equal counts by ascending slot (a stable counting sort) --
          * so every batch-mate in front of a node exists on all of that node's levels.  Per task: the exact top-batch_k
          * of the rows in front of the node by (distance ascending, position DESCENDING) -- the exact-search order --
-         * among the rows strictly closer than the task's worst list entry when its list is full (anything else could
-         * not enter the list). */
+         * among the rows strictly closer than the task's list entry at rank min(ef, SEED_RANK) (when the list is that
+         * long). */
         const uint32_t bk = ix->batch_k;
         uint64_t* mates = NULL;  /* per task: bk keys (distance bits << 32 | slot), ascending; ~0 padding */
         if (bk) {
@@ -461,7 +462,8 @@ BM_EXPORT void bm_build(bm_index* ix, uint64_t upto, uint64_t max_batches) {
                 size_t task = task_base[t];
                 uint64_t top[64]; /* keys: distance bits << 32 | ~position, ascending */
                 for (int l = lq < ix->max_level ? lq : ix->max_level; l >= 0; --l, ++task) {
-                    uint32_t tau = lens[task] == ef ? (uint32_t)(lists[task * ef + ef - 1] >> 32) : 0xFFFFFFFFu;
+                    const uint32_t seed_rank = ef < SEED_RANK ? ef : SEED_RANK;
+                    uint32_t tau = lens[task] >= seed_rank ? (uint32_t)(lists[task * ef + seed_rank - 1] >> 32) : 0xFFFFFFFFu;
                     uint32_t nt = 0;
                     for (uint64_t p2 = 0; p2 < pos; ++p2) {
                         uint32_t bits = dist_bits(q, ix->vecs + (size_t)(s + order[p2]) * 128);
