@@ -140,6 +140,13 @@ RB_EXPORT void rb_unpack_topk_device(void const* d_keys, uint64_t query_count, u
 RB_EXPORT void rb_synth_fingerprints_device(void* d_out, uint64_t first_row, uint64_t rows, uint64_t seed,
                                             void const* d_centres, uint32_t centre_count, int edge_cases,
                                             uintptr_t stream, rb_error_t* error);
+/* the same generator with its optional modes: rows_per_centre > 0 = analogue-series order (the rows of a cluster are
+ * contiguous: row r belongs to centre (r / rows_per_centre) mod centre_count); dup_fold > 1 = runs of dup_fold exact
+ * duplicates inside [dup_start, dup_start + dup_rows) */
+RB_EXPORT void rb_synth_fingerprints_device_ex(void* d_out, uint64_t first_row, uint64_t rows, uint64_t seed,
+                                               void const* d_centres, uint32_t centre_count, int edge_cases,
+                                               uint64_t rows_per_centre, uint64_t dup_fold, uint64_t dup_start,
+                                               uint64_t dup_rows, uintptr_t stream, rb_error_t* error);
 
 /* ---------------------------------------------------------------- serialisation: python/lib.cpp:940-954,
  * index_dense.hpp:1025-1093 (save), 1114-1259 (load), 1267-1415 (view), index.hpp:3236-3277, 3463-3532 */

@@ -14,6 +14,14 @@ if [ ! -d "$REF/include/usearch" ]; then
 fi
 EXT="$($PY -c 'import sysconfig;print(sysconfig.get_config_var("EXT_SUFFIX"))')"
 mkdir -p "$OUT"
+# RAD itself is pure Python above the index: its UNMODIFIED modules are staged next to the binding (git-ignored, like
+# the rest of oracle/_ref) so that the GPU box -- which has no /root/reference -- can run the reference's traverser
+# and services over a GPU-built index (tests/test_rad_gpu_e2e.py)
+RAD_SRC="${RAD_REFERENCE_ROOT:-/root/reference}/rad"
+if [ -d "$RAD_SRC" ]; then
+  mkdir -p "$HERE/_ref/rad"
+  cp "$RAD_SRC"/*.py "$HERE/_ref/rad"/
+fi
 if [ -f "$OUT/compiled$EXT" ] && [ "$OUT/compiled$EXT" -nt "$REF/python/lib.cpp" ] && [ -z "${FORCE:-}" ]; then
   echo "build_ref: $OUT/compiled$EXT up to date"; exit 0
 fi

@@ -84,6 +84,9 @@ SIGNATURES = {
                                      C.c_size_t, _ERR]),
     "rb_synth_fingerprints_device": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32,
                                             C.c_int, C.c_size_t, _ERR]),
+    "rb_synth_fingerprints_device_ex": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32,
+                                               C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_size_t,
+                                               _ERR]),
     "rb_save": (None, [_H, C.c_char_p, C.c_int, _ERR]),
     "rb_load": (None, [_H, C.c_char_p, C.c_int, _ERR]),
     "rb_view": (None, [_H, C.c_char_p, C.c_int, _ERR]),

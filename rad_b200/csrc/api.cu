@@ -1639,14 +1639,23 @@ void rb_unpack_topk_device(void const* d_keys, uint64_t query_count, uint32_t k,
 
 void rb_synth_fingerprints_device(void* d_out, uint64_t first_row, uint64_t rows, uint64_t seed, void const* d_centres,
                                   uint32_t centre_count, int edge_cases, uintptr_t stream, rb_error_t* error) {
+    rb_synth_fingerprints_device_ex(d_out, first_row, rows, seed, d_centres, centre_count, edge_cases, 0, 0, 0, 0, stream,
+                                    error);
+}
+
+void rb_synth_fingerprints_device_ex(void* d_out, uint64_t first_row, uint64_t rows, uint64_t seed, void const* d_centres,
+                                     uint32_t centre_count, int edge_cases, uint64_t rows_per_centre, uint64_t dup_fold,
+                                     uint64_t dup_start, uint64_t dup_rows, uintptr_t stream, rb_error_t* error) {
     if (error)
         *error = nullptr;
     if (!rows)
         return;
+    if (!centre_count)
+        RB_FAIL("the centre table is empty");
     uint64_t threads = rows * 32;
     rb::synth_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
         static_cast<uint32_t*>(d_out), first_row, rows, seed, static_cast<uint32_t const*>(d_centres), centre_count,
-        edge_cases);
+        edge_cases, rb::SynthModes{rows_per_centre, dup_fold, dup_start, dup_rows});
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
         RB_FAIL(std::string("CUDA error in synth: ") + cudaGetErrorString(e));

@@ -21,10 +21,20 @@ __device__ __forceinline__ uint64_t splitmix64(uint64_t x) {
     return x;
 }
 
+// The generator's optional modes (rad_b200/synth.py: clustered_fingerprints): rows_per_centre > 0 = the analogue-series
+// order (row r belongs to centre (r / rows_per_centre) mod C: the rows of a cluster are contiguous); dup_fold > 1 = runs
+// of dup_fold exact duplicates inside [dup_start, dup_start + dup_rows).
+struct SynthModes {
+    uint64_t rows_per_centre, dup_fold, dup_start, dup_rows;
+};
+
 __device__ __forceinline__ uint32_t synth_word(uint64_t row, uint32_t w, uint64_t seed, const uint32_t* centres,
-                                               uint32_t centre_count) {
+                                               uint32_t centre_count, SynthModes md) {
     const uint64_t base = seed * kSynthGold;
-    uint32_t assign = (uint32_t)(splitmix64(base + row + 0xA55Aull) % centre_count);
+    if (md.dup_fold > 1 && row >= md.dup_start && row < md.dup_start + md.dup_rows)
+        row = md.dup_start + (row - md.dup_start) / md.dup_fold * md.dup_fold;
+    uint32_t assign = md.rows_per_centre ? (uint32_t)((row / md.rows_per_centre) % centre_count)
+                                         : (uint32_t)(splitmix64(base + row + 0xA55Aull) % centre_count);
     uint32_t cw = centres[(size_t)assign * 32 + w];
     uint32_t word = 0;
 #pragma unroll 4
@@ -41,7 +51,7 @@ __device__ __forceinline__ uint32_t synth_word(uint64_t row, uint32_t w, uint64_
 
 // one thread per 32-bit word: out is rows x 32 words
 __global__ void synth_kernel(uint32_t* out, uint64_t first_row, uint64_t rows, uint64_t seed, const uint32_t* centres,
-                             uint32_t centre_count, int edge_cases) {
+                             uint32_t centre_count, int edge_cases, SynthModes md) {
     uint64_t gid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= rows * 32)
         return;
@@ -51,7 +61,7 @@ __global__ void synth_kernel(uint32_t* out, uint64_t first_row, uint64_t rows, u
     if (edge_cases && row == 0)
         word = 0;
     else
-        word = synth_word((edge_cases && row == 1) ? 2 : row, w, seed, centres, centre_count);
+        word = synth_word((edge_cases && row == 1) ? 2 : row, w, seed, centres, centre_count, md);
     out[gid] = word;
 }
 

@@ -148,3 +148,46 @@ def heldout_queries(q: int, seed: int = 0, *, n_total: int, ndim: int = NDIM) ->
     """Q held-out rows drawn from the same centres as the database of ``n_total`` rows (config 3): they are rows
     [2^40, 2^40 + q) of the same counter-based stream, which no database shard ever reaches."""
     return clustered_fingerprints(q, seed, start=1 << 40, n_total=n_total, ndim=ndim, edge_cases=False)
+
+
+def set_spec(kind: str, n_total: int, seed: int = 0) -> tuple[np.ndarray, dict]:
+    """(centre table, generator arguments) of a named workload: 'sparse' = SURVEY.md §8d (n/100 centres, hashed),
+    'dense' = the routable set (1000 centres), 'analogue' = the adversarial analogue-series set."""
+    if kind == "sparse":
+        return centre_table(seed, n_total), {}
+    if kind == "dense":
+        return centre_table(seed, n_total, count=1000), {}
+    if kind == "analogue":
+        return (centre_table(seed, n_total, count=max(1, n_total // ANALOGUE_ROWS_PER_CENTRE)),
+                analogue_params(n_total))
+    raise ValueError(f"unknown workload {kind!r}")
+
+
+def named_set(kind: str, n: int, seed: int = 0, *, start: int = 0, n_total: int | None = None) -> np.ndarray:
+    """numpy rows [start, start + n) of a named workload."""
+    n_total = start + n if n_total is None else n_total
+    centres, modes = set_spec(kind, n_total, seed)
+    return clustered_fingerprints(n, seed, start=start, n_total=n_total, centres=centres, **modes)
+
+
+def named_set_device(kind: str, n: int, seed: int = 0, *, start: int = 0, n_total: int | None = None, device=None):
+    """The same rows generated ON THE DEVICE (rb_synth_fingerprints_device_ex) -> torch.uint8 [n, 128] cuda tensor."""
+    import ctypes as C
+
+    import torch
+
+    from . import _native
+    n_total = start + n if n_total is None else n_total
+    centres, modes = set_spec(kind, n_total, seed)
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    d_c = torch.from_numpy(centres).to(dev)
+    out = torch.empty((n, ROW_BYTES), dtype=torch.uint8, device=dev)
+    err = C.c_char_p()
+    with torch.cuda.device(dev):
+        _native.lib().rb_synth_fingerprints_device_ex(
+            out.data_ptr(), start, n, seed, d_c.data_ptr(), len(centres), 1, modes.get("rows_per_centre", 0),
+            modes.get("dup_fold", 0), modes.get("dup_start", 0), modes.get("dup_rows", 0),
+            torch.cuda.current_stream(dev).cuda_stream, C.byref(err))
+        _native.check(err)
+        torch.cuda.synchronize(dev)
+    return out

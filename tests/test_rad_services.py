@@ -1,12 +1,11 @@
-"""RAD's own service layer (UNMODIFIED rad/hnsw_service.py and rad/hnsw_server.py, imported from /root/reference) on
+"""RAD's own service layer (UNMODIFIED rad/hnsw_service.py and rad/hnsw_server.py, imported from the reference tree) on
 top of rad_b200.index.Index, beside the same services on top of the reference's usearch Index, on the same `.usearch`
 file.  This is the duck-typed contract of SURVEY.md §8b: RAD reads the graph through `get_neighbors`,
 `get_top_level_nodes`, `len`, `max_level`, `levels_stats`, ... and nothing else (rad/hnsw_service.py:219-232, 400-412;
 rad/hnsw_server.py:148-161, 196, 471-483, 593-602).
 
-CPU only (graph reads never touch CUDA) and only where /root/reference exists: the GPU box has neither, and the
-`-m gpu` suite pins the files the GPU build writes to the format these services read
-(tests/test_gpu_build.py::test_structural_invariants_and_file_round_trip)."""
+CPU only (graph reads never touch CUDA), over the reference-built golden file.  The same services over an index the
+GPU BUILT are exercised on the GPU box by tests/test_rad_gpu_e2e.py."""
 import multiprocessing
 import os
 import socket
@@ -16,9 +15,10 @@ import time
 import numpy as np
 import pytest
 
-REFERENCE = "/root/reference"
-pytestmark = pytest.mark.skipif(not os.path.isdir(os.path.join(REFERENCE, "rad")),
-                                reason="the reference tree is not present on this machine")
+from tests.refpath import rad_root
+
+REFERENCE = rad_root()
+pytestmark = pytest.mark.skipif(REFERENCE is None, reason="the reference's rad package is not present on this machine")
 
 
 @pytest.fixture(scope="module")

@@ -3,7 +3,7 @@ walking a graph served by rad_b200.index.Index, beside the same traversal over t
 same `.usearch` file.  One worker makes the walk deterministic, so the two scored sequences must be identical.
 
 The container has no `redis` wheel and no redis-server: tests/fake_redis.py stands in for the client package (test
-infrastructure only).  Skipped where /root/reference is absent (the GPU box)."""
+infrastructure only).  The walk over a GPU-BUILT index runs on the GPU box: tests/test_rad_gpu_e2e.py."""
 import os
 import sqlite3
 import sys
@@ -11,9 +11,10 @@ import zlib
 
 import pytest
 
-REFERENCE = "/root/reference"
-pytestmark = pytest.mark.skipif(not os.path.isdir(os.path.join(REFERENCE, "rad")),
-                                reason="the reference tree is not present on this machine")
+from tests.refpath import rad_root
+
+REFERENCE = rad_root()
+pytestmark = pytest.mark.skipif(REFERENCE is None, reason="the reference's rad package is not present on this machine")
 
 
 @pytest.fixture(scope="module")
