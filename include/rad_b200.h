@@ -51,6 +51,9 @@ typedef struct rb_init_options {
     uint32_t bloom_bits_log2;  /* visited filter size per traversal (bits, log2); 0 -> 15                     */
     uint32_t debug_max_batches;/* stop an rb_add after this many batches (0 = unlimited); tests only          */
     uint32_t no_batch_tile;    /* 1: skip the batch tile (the nodes of a batch stay blind to each other); A/B only */
+    uint32_t connectivity_base;/* level-0 row width; 0 -> 2 x connectivity (what the file format and the reference use).
+                                * Another value is only meant for the upper-level sub-build of the cross-shard stitch
+                                * (level l of the graph = level l - 1 of that build) and cannot be saved                */
 } rb_init_options_t;
 
 /* per-level statistics: usearch python/lib.cpp:1007-1013 (IndexStats), index.hpp:3087-3179 */
@@ -100,6 +103,13 @@ RB_EXPORT void rb_add(rb_index_t* index, uint64_t const* keys, uint8_t const* ve
  * 16-byte aligned, zero-padded past dimensions/8; `keys` is a host pointer or NULL (size .. size+count-1). */
 RB_EXPORT void rb_add_device(rb_index_t* index, uint64_t const* keys, void const* d_vectors, size_t count,
                              rb_error_t* error);
+/* rb_add_device with PRESCRIBED levels (host pointer, one per row) instead of the level stream: the upper-level sub-build
+ * of the cross-shard stitch */
+RB_EXPORT void rb_add_device_levels(rb_index_t* index, uint64_t const* keys, void const* d_vectors, size_t count,
+                                    int16_t const* levels, rb_error_t* error);
+/* a row shard of a larger build: this EMPTY index starts the reference's single level stream (index.hpp:3867-3871) at
+ * row `first_row`, so its nodes get the levels a one-piece build would give those rows */
+RB_EXPORT void rb_seek_level_stream(rb_index_t* index, uint64_t first_row, rb_error_t* error);
 RB_EXPORT void rb_sync_host(rb_index_t* index, rb_error_t* error);
 /* Index.clear(): forget every node but keep the reserved host and device memory (index.py:1150-1152 ->
  * index_dense.hpp:989-998 clear(): "erases all vectors from the index, preserving the allocated space") */
@@ -147,6 +157,32 @@ RB_EXPORT void rb_synth_fingerprints_device_ex(void* d_out, uint64_t first_row, 
                                                void const* d_centres, uint32_t centre_count, int edge_cases,
                                                uint64_t rows_per_centre, uint64_t dup_fold, uint64_t dup_start,
                                                uint64_t dup_rows, uintptr_t stream, rb_error_t* error);
+
+/* ---------------------------------------------------------------- one graph from G row shards (SURVEY.md section 8e row 3;
+ * usearch has no counterpart: its multi-index `Indexes`, python/lib.cpp:417-498, only searches shards side by side).
+ * Every shard is built on its own GPU; then every node searches the OTHER shards (rb_search_device on their handles),
+ * the answers travel with their fingerprints (rb_gather_vectors_device; NCCL all-gather / all-to-all between the
+ * processes -- rad_b200/sharded.py), and rb_stitch_device prunes own links + remote candidates with the reference's
+ * heuristic (index.hpp:4246-4289) into level-0 rows in GLOBAL slots.  rb_import_graph assembles the global index.
+ * All pointers named d_* are device pointers; the calls run on the handle's stream and return when done. */
+/* d_out[i] = fingerprint (128 bytes) of local slot d_slots[i] (u32; 0xFFFFFFFF -> zeros) */
+RB_EXPORT void rb_gather_vectors_device(rb_index_t* index, void const* d_slots, uint64_t count, void* d_out,
+                                        rb_error_t* error);
+/* d_out = fingerprints of local slots [first, first + count), 128 bytes each */
+RB_EXPORT void rb_copy_vectors_device(rb_index_t* index, uint64_t first, uint64_t count, void* d_out, rb_error_t* error);
+/* level-0 rows of local nodes [first, first + count) after the stitch -> d_rows_out (u32 [count x 2M], GLOBAL slots,
+ * 0xFFFFFFFF padded).  d_cand_slots: u32 [count x cands] GLOBAL slots of the remote candidates (0xFFFFFFFF = none),
+ * d_cand_vectors: their fingerprints [count x cands x 128 bytes]; cands <= 128 - 2M.  slot_base = global slot of this
+ * shard's local slot 0.  The shard's own graph is not modified. */
+RB_EXPORT void rb_stitch_device(rb_index_t* index, uint64_t first, uint64_t count, uint64_t slot_base,
+                                void const* d_cand_slots, void const* d_cand_vectors, uint32_t cands, void* d_rows_out,
+                                rb_error_t* error);
+/* replace the graph of `index` by one assembled elsewhere: host arrays keys u64[n], levels i16[n], adj0 u32[n x 2M],
+ * adj_upper u32[sum(levels) x M] (a node's rows consecutive, level 1 first), vectors u8[n x dimensions/8] or NULL,
+ * entry = a node of the top level.  Afterwards the index saves / serves / searches like one built in one piece. */
+RB_EXPORT void rb_import_graph(rb_index_t* index, uint64_t const* keys, int16_t const* levels, uint32_t const* adj0,
+                               uint32_t const* adj_upper, uint8_t const* vectors, size_t n, uint64_t entry,
+                               rb_error_t* error);
 
 /* ---------------------------------------------------------------- serialisation: python/lib.cpp:940-954,
  * index_dense.hpp:1025-1093 (save), 1114-1259 (load), 1267-1415 (view), index.hpp:3236-3277, 3463-3532 */

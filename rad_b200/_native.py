@@ -26,6 +26,7 @@ class InitOptions(C.Structure):
         ("bloom_bits_log2", C.c_uint32),
         ("debug_max_batches", C.c_uint32),
         ("no_batch_tile", C.c_uint32),
+        ("connectivity_base", C.c_uint32),
     ]
 
 
@@ -87,6 +88,14 @@ SIGNATURES = {
     "rb_synth_fingerprints_device_ex": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint32,
                                                C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_size_t,
                                                _ERR]),
+    "rb_add_device_levels": (None, [_H, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, _ERR]),
+    "rb_seek_level_stream": (None, [_H, C.c_uint64, _ERR]),
+    "rb_gather_vectors_device": (None, [_H, C.c_void_p, C.c_uint64, C.c_void_p, _ERR]),
+    "rb_copy_vectors_device": (None, [_H, C.c_uint64, C.c_uint64, C.c_void_p, _ERR]),
+    "rb_stitch_device": (None, [_H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint32,
+                                C.c_void_p, _ERR]),
+    "rb_import_graph": (None, [_H, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                               C.c_uint64, _ERR]),
     "rb_save": (None, [_H, C.c_char_p, C.c_int, _ERR]),
     "rb_load": (None, [_H, C.c_char_p, C.c_int, _ERR]),
     "rb_view": (None, [_H, C.c_char_p, C.c_int, _ERR]),

@@ -988,7 +988,8 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
 }
 
 std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_vectors, size_t stride,
-                       void const* device_vectors, size_t n, rb_progress_t progress, void* user) {
+                       void const* device_vectors, size_t n, rb_progress_t progress, void* user,
+                       int16_t const* forced_levels = nullptr) {
     rbh::HostIndex& h = ix->host;
     if (h.immutable())
         return "Can't add to an immutable index";
@@ -1015,7 +1016,15 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
         return err;
     std::vector<int16_t> new_levels;
     const uint32_t rng_before = h.level_rng;
-    h.draw_levels(n, new_levels);
+    h.draw_levels(n, new_levels);  // (the stream advances either way: an index stays in step with its size)
+    if (forced_levels) {
+        for (size_t i = 0; i < n; ++i)
+            if (forced_levels[i] < 0) {
+                h.level_rng = rng_before;
+                return "levels must not be negative";
+            }
+        new_levels.assign(forced_levels, forced_levels + n);
+    }
     pt.mark("device ready + level stream");
     uint64_t upper = h.upper_off[old_size];
     int16_t top_new = 0;
@@ -1379,6 +1388,10 @@ rb_index_t* rb_init(rb_init_options_t const* options, rb_error_t* error) {
         set_error(error, "connectivity must be in 2..16");
         return nullptr;
     }
+    if (o.connectivity_base && (o.connectivity_base < o.connectivity || o.connectivity_base > (uint32_t)rb::kMaxWidth)) {
+        set_error(error, "connectivity_base must be in connectivity..32");
+        return nullptr;
+    }
     if (!o.expansion_add)
         o.expansion_add = 128;
     if (!o.expansion_search)
@@ -1402,7 +1415,7 @@ rb_index_t* rb_init(rb_init_options_t const* options, rb_error_t* error) {
     ix->host.ndim = o.dimensions;
     ix->host.vec_bytes = (uint32_t)(o.dimensions / 8);
     ix->host.m = o.connectivity;
-    ix->host.m0 = 2 * o.connectivity;
+    ix->host.m0 = o.connectivity_base ? o.connectivity_base : 2 * o.connectivity;
     ix->host.ef_add = o.expansion_add;
     ix->host.ef_search = o.expansion_search;
     ix->host.upper_off.assign(1, 0);
@@ -1468,6 +1481,119 @@ void rb_add_device(rb_index_t* ix, uint64_t const* keys, void const* d_vectors, 
     std::string err = add_common(ix, keys, nullptr, 128, d_vectors, count, nullptr, nullptr);
     if (!err.empty())
         RB_FAIL(err);
+}
+
+void rb_add_device_levels(rb_index_t* ix, uint64_t const* keys, void const* d_vectors, size_t count,
+                          int16_t const* levels, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (count && (!d_vectors || !levels))
+        RB_FAIL("Expects a matrix of vectors and their levels!");
+    std::string err = add_common(ix, keys, nullptr, 128, d_vectors, count, nullptr, nullptr, levels);
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+void rb_seek_level_stream(rb_index_t* ix, uint64_t first_row, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (ix->host.size())
+        RB_FAIL("the level stream can only be positioned on an empty index");
+    ix->host.seek_level_stream(first_row);
+}
+
+void rb_gather_vectors_device(rb_index_t* ix, void const* d_slots, uint64_t count, void* d_out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!count)
+        return;
+    std::string err = prepare_search(ix, 1);
+    if (!err.empty())
+        RB_FAIL(err);
+    DeviceState& d = ix->dev;
+    const unsigned grid = (unsigned)std::min<uint64_t>((count * 8 + 255) / 256, (uint64_t)d.sm_count * 16);
+    rb::gather_rows_kernel<<<grid, 256, 0, d.stream>>>(d.fp, static_cast<uint32_t const*>(d_slots), count,
+                                                       static_cast<uint4*>(d_out));
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(d.stream);
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in gather: ") + cudaGetErrorString(e));
+}
+
+void rb_copy_vectors_device(rb_index_t* ix, uint64_t first, uint64_t count, void* d_out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!count)
+        return;
+    std::string err = prepare_search(ix, 1);
+    if (!err.empty())
+        RB_FAIL(err);
+    if (first + count > ix->host.size())
+        RB_FAIL("rows out of range");
+    DeviceState& d = ix->dev;
+    cudaError_t e = cudaMemcpyAsync(d_out, reinterpret_cast<uint8_t const*>(d.fp) + first * 128, count * 128,
+                                    cudaMemcpyDeviceToDevice, d.stream);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(d.stream);
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in copy: ") + cudaGetErrorString(e));
+}
+
+void rb_stitch_device(rb_index_t* ix, uint64_t first, uint64_t count, uint64_t slot_base, void const* d_cand_slots,
+                      void const* d_cand_vectors, uint32_t cands, void* d_rows_out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!count)
+        return;
+    std::string err = prepare_search(ix, 1);
+    if (!err.empty())
+        RB_FAIL(err);
+    if (first + count > ix->host.size())
+        RB_FAIL("rows out of range");
+    if (cands + ix->host.m0 > (uint32_t)rb::kStitchMax)
+        RB_FAIL("too many remote candidates per node (own links + candidates must fit 128)");
+    if (slot_base + ix->host.size() > (1ull << 32))
+        RB_FAIL("global slots must fit 32 bits");
+    DeviceState& d = ix->dev;
+    rb::StitchParams sp;
+    sp.g = graph_view(ix);
+    sp.first = (uint32_t)first;
+    sp.count = (uint32_t)count;
+    sp.slot_base = (uint32_t)slot_base;
+    sp.cand_slots = static_cast<uint32_t const*>(d_cand_slots);
+    sp.cand_fp = static_cast<uint4 const*>(d_cand_vectors);
+    sp.cands = cands;
+    sp.rows_out = static_cast<uint32_t*>(d_rows_out);
+    sp.counters = nullptr;
+    const unsigned grid = (unsigned)std::min<uint64_t>((count + rb::kWarpsPerBlock - 1) / rb::kWarpsPerBlock,
+                                                       (uint64_t)d.sm_count * 8);
+    rb::stitch_kernel<<<grid, rb::kWarpsPerBlock * 32, 0, d.stream>>>(sp);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(d.stream);
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in stitch: ") + cudaGetErrorString(e));
+}
+
+void rb_import_graph(rb_index_t* ix, uint64_t const* keys, int16_t const* levels, uint32_t const* adj0,
+                     uint32_t const* adj_upper, uint8_t const* vectors, size_t n, uint64_t entry, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (ix->host.viewing)
+        RB_FAIL("Can't import into an immutable index");
+    std::string err = ix->host.import_graph(keys, levels, adj0, adj_upper, vectors, n, entry);
+    if (!err.empty())
+        RB_FAIL(err);
+    // the device copy (if any) belongs to the old graph: start from fresh arrays at the next device call
+    if (ix->dev.device >= 0) {
+        int dev = ix->dev.device;
+        ix->dev.release();
+        ix->opts.device = dev;
+    }
+    ix->device_graph_valid = false;
+    ix->host_graph_valid = true;
+    ix->last = rb_counters_t{};
 }
 
 void rb_clear(rb_index_t* ix, rb_error_t* error) {
@@ -1693,6 +1819,8 @@ extern "C" {
 void rb_save(rb_index_t* ix, char const* path, int exclude_vectors, rb_error_t* error) {
     if (error)
         *error = nullptr;
+    if (ix->host.m0 != 2 * ix->host.m)
+        RB_FAIL("an index with a non-standard connectivity_base cannot be saved (the reader expects 2 x connectivity)");
     std::string err = sync_host(ix);
     if (!err.empty())
         RB_FAIL(err);

@@ -544,9 +544,12 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
 // `q4` is the slice (lane & 7) of the fingerprint the candidates' keys were measured from: the test
 // d(c, s) < d(c, q) is done on the integer counts, i_cs * u_cq > i_cq * u_cs, which is the same decision as comparing
 // the order keys (they are strictly monotone in i / u and equal for equal ratios) without a divide per pair.
-__device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, const WarpScratch& w, const uint64_t* cand,
-                                                          uint32_t count, uint32_t needed, TraversalCounters& tc,
-                                                          uint4 q4) {
+// `fetch(key, sub)` returns slice `sub` of the fingerprint a candidate key stands for (the graph's own rows by default;
+// the cross-shard stitch also feeds candidates that live in a staging buffer).
+template <typename Fetch>
+__device__ __forceinline__ uint32_t warp_select_neighbors_from(const WarpScratch& w, const uint64_t* cand, uint32_t count,
+                                                               uint32_t needed, TraversalCounters& tc, uint4 q4,
+                                                               Fetch fetch) {
     const int lane = threadIdx.x & 31, sub = lane & 7, grp = lane >> 3;
     if (count < needed) {
         for (uint32_t i = lane; i < count; i += 32)
@@ -561,7 +564,7 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
     // the closest candidate is always kept
     {
         uint64_t k0 = cand[0];
-        const uint4 a0 = load_slice(g.fp, key_slot(k0), sub);
+        const uint4 a0 = fetch(k0, sub);
         if (lane < 8)
             w.kept[sub] = a0;
         if (lane == 0)
@@ -576,7 +579,7 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
         uint32_t ci = c + grp;  // each group of 8 lanes examines one candidate
         bool have = ci < count;
         uint64_t ck = have ? cand[ci] : 0ull;
-        uint4 a = have ? load_slice(g.fp, key_slot(ck), sub) : make_uint4(0, 0, 0, 0);
+        uint4 a = have ? fetch(ck, sub) : make_uint4(0, 0, 0, 0);
         bool good = have;
         const uint32_t vq = group8_sum(popc4_and(a, q4) | (popc4(a) << 16));
         const uint32_t icq = vq & 0xFFFFu, pa = vq >> 16;
@@ -610,6 +613,14 @@ __device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, co
         c += (uint32_t)first + 1;
     }
     return kept;
+}
+
+__device__ __forceinline__ uint32_t warp_select_neighbors(const GraphView& g, const WarpScratch& w, const uint64_t* cand,
+                                                          uint32_t count, uint32_t needed, TraversalCounters& tc,
+                                                          uint4 q4) {
+    const uint4* fp = g.fp;
+    return warp_select_neighbors_from(w, cand, count, needed, tc, q4,
+                                      [fp](uint64_t key, int sub) { return load_slice(fp, key_slot(key), sub); });
 }
 
 // ------------------------------------------------------------------------------------------------ insertion
@@ -981,6 +992,113 @@ __global__ void __launch_bounds__(256) link_popcount_kernel(const uint32_t* __re
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < links; i += (size_t)gridDim.x * blockDim.x) {
         const uint32_t id = __ldg(adj + i);
         out[i] = id == RB_EMPTY ? (uint16_t)0 : __ldg(node_pc + id);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ cross-shard stitch
+// G row shards are built independently (one per GPU); afterwards every node has searched the OTHER shards' graphs and
+// received their nearest rows (global slots + fingerprints).  One warp per node: the node's own
+// level-0 links and the remote candidates are ordered by (distance, global slot) and pruned by the reference's heuristic
+// (index.hpp:4246-4289), needed = the row width -- what form_reverse_links_ does when a full row receives new links
+// (index.hpp:3816-3865) -- and the row is emitted in GLOBAL slots.  The shard's own graph is NOT modified: the other
+// shards are still searching it.  CPU statement: tests/model/batched_model.c: bm_stitch_rows.
+constexpr int kStitchMax = 128;  // own links + remote candidates per node
+
+struct StitchParams {
+    GraphView g;                 // this shard: fingerprints and level-0 rows in LOCAL slots
+    uint32_t first, count;       // local nodes [first, first + count)
+    uint32_t slot_base;          // global slot of local slot 0
+    const uint32_t* cand_slots;  // [count x cands]  GLOBAL slots of the remote candidates, RB_EMPTY = none
+    const uint4* cand_fp;        // [count x cands x 8]  their fingerprints
+    uint32_t cands;              // <= kStitchMax - m0
+    uint32_t* rows_out;          // [count x m0]  GLOBAL slots, RB_EMPTY padded
+    unsigned long long* counters;
+};
+
+__global__ void __launch_bounds__(kWarpsPerBlock * 32) stitch_kernel(StitchParams p) {
+    constexpr int kPerWarp = kStitchMax * 8 * 2 + kMaxWidth * 128 + kMaxWidth * 8 + kStitchMax * 2;
+    __shared__ __align__(16) unsigned char smem[kWarpsPerBlock * kPerWarp];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, grp = lane >> 3;
+    unsigned char* base = smem + (size_t)warp * kPerWarp;
+    uint64_t* ckey = reinterpret_cast<uint64_t*>(base);  // order bits << 32 | global slot, unsorted
+    uint64_t* sorted = ckey + kStitchMax;                // order bits << 32 | candidate index << 1, ascending
+    WarpScratch w;
+    w.kept = reinterpret_cast<uint4*>(base + kStitchMax * 16);
+    w.sel = reinterpret_cast<uint64_t*>(base + kStitchMax * 16 + kMaxWidth * 128);
+    // column of cand_slots a compacted remote entry came from
+    uint16_t* origin = reinterpret_cast<uint16_t*>(base + kStitchMax * 16 + kMaxWidth * 128 + kMaxWidth * 8);
+    w.list = nullptr, w.bloom = nullptr, w.pend = nullptr, w.ids = nullptr, w.bloom_log2 = 0;
+    TraversalCounters tc{0, 0};
+    for (uint32_t t = blockIdx.x * kWarpsPerBlock + warp; t < p.count; t += gridDim.x * kWarpsPerBlock) {
+        const uint32_t node = p.first + t;
+        const uint4 q4 = load_slice(p.g.fp, node, sub);
+        const uint32_t m0 = p.g.m0;
+        const uint32_t* row = p.g.adj0 + (size_t)node * m0;
+        const uint32_t own = (uint32_t)lane < m0 ? row[lane] : RB_EMPTY;
+        const uint32_t deg = __popc(__ballot_sync(RB_FULL_MASK, own != RB_EMPTY));  // rows are packed at the front
+        {
+            const uint32_t bits = warp_eval(p.g.fp, q4, own, deg);
+            if ((uint32_t)lane < deg)
+                ckey[lane] = ((uint64_t)bits << 32) | (uint64_t)(own + p.slot_base);
+        }
+        // remote candidates: their fingerprints travelled with them; four per round, 8 lanes each
+        uint32_t n = deg;
+        const uint32_t* cs = p.cand_slots + (size_t)t * p.cands;
+        const uint4* cf = p.cand_fp + (size_t)t * p.cands * 8;
+        for (uint32_t c0 = 0; c0 < p.cands; c0 += 4) {
+            const uint32_t c = c0 + grp;
+            const uint32_t gs = c < p.cands ? cs[c] : RB_EMPTY;
+            const uint4 a = gs != RB_EMPTY ? __ldg(cf + (size_t)c * 8 + sub) : make_uint4(0, 0, 0, 0);
+            const uint32_t v = group8_inter_union(a, q4);
+            const uint32_t bits = order_key_bits(v & 0xFFFFu, v >> 16);
+            const uint32_t mask = __ballot_sync(RB_FULL_MASK, gs != RB_EMPTY && sub == 0);  // bit 8 * grp
+            if (gs != RB_EMPTY && sub == 0) {
+                const uint32_t at = n + __popc(mask & ((1u << lane) - 1u));
+                ckey[at] = ((uint64_t)bits << 32) | gs;
+                origin[at] = (uint16_t)c;
+            }
+            n += __popc(mask);
+        }
+        tc.distances += n;
+        __syncwarp();
+        // rank by counting (keys are unique: a global slot appears once), carrying the candidate's index along
+        for (uint32_t i = lane; i < n; i += 32) {
+            const uint64_t mine = ckey[i];
+            uint32_t rank = 0;
+            for (uint32_t j = 0; j < n; ++j)
+                rank += ckey[j] < mine;
+            sorted[rank] = (mine & 0xFFFFFFFF00000000ull) | ((uint64_t)i << 1);
+        }
+        __syncwarp();
+        const uint4* own_fp = p.g.fp;
+        const uint32_t base_slot = p.slot_base;
+        auto fetch = [own_fp, base_slot, ckey, origin, cf, deg](uint64_t key, int sl) -> uint4 {
+            const uint32_t idx = (uint32_t)(key >> 1) & 0x7FFFFFFFu;
+            if (idx < deg)
+                return load_slice(own_fp, (uint32_t)ckey[idx] - base_slot, sl);
+            return __ldg(cf + (size_t)origin[idx] * 8 + sl);
+        };
+        const uint32_t ns = warp_select_neighbors_from(w, sorted, n, m0, tc, q4, fetch);
+        if ((uint32_t)lane < m0) {
+            uint32_t out = RB_EMPTY;
+            if ((uint32_t)lane < ns)
+                out = (uint32_t)ckey[(uint32_t)(w.sel[lane] >> 1) & 0x7FFFFFFFu];
+            p.rows_out[(size_t)t * m0 + lane] = out;
+        }
+        __syncwarp();
+    }
+    if (lane == 0 && p.counters)
+        atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+}
+
+// out[i] = fingerprint of local slot slots[i] (RB_EMPTY -> zeros): 8 lanes per row
+__global__ void __launch_bounds__(256) gather_rows_kernel(const uint4* __restrict__ fp, const uint32_t* __restrict__ slots,
+                                                          uint64_t count, uint4* __restrict__ out) {
+    const uint32_t sub = threadIdx.x & 7;
+    for (uint64_t i = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3; i < count;
+         i += ((uint64_t)gridDim.x * blockDim.x) >> 3) {
+        const uint32_t s = __ldg(slots + i);
+        out[i * 8 + sub] = s == RB_EMPTY ? make_uint4(0, 0, 0, 0) : __ldg(fp + (size_t)s * 8 + sub);
     }
 }
 

@@ -150,6 +150,60 @@ void HostIndex::draw_levels(size_t n, std::vector<int16_t>& out) {
     level_rng = minstd_skip(level_rng, 2 * (uint64_t)n);
 }
 
+void HostIndex::seek_level_stream(uint64_t first_row) { level_rng = minstd_skip(1u, 2 * first_row); }
+
+std::string HostIndex::import_graph(uint64_t const* new_keys, int16_t const* new_levels, uint32_t const* new_adj0,
+                                    uint32_t const* new_adju, uint8_t const* vectors, size_t n, uint64_t new_entry) {
+    if (n && new_entry >= n)
+        return "import: the entry slot is out of range";
+    int top = 0;
+    uint64_t upper = 0;
+    for (size_t i = 0; i < n; ++i) {
+        if (new_levels[i] < 0)
+            return "import: negative level";
+        upper += (uint64_t)new_levels[i];
+        top = std::max<int>(top, new_levels[i]);
+    }
+    if (n && new_levels[new_entry] != top)
+        return "import: the entry slot is not a node of the top level";
+    for (size_t i = 0; i < n * (size_t)m0; ++i)
+        if (new_adj0[i] != kEmpty && new_adj0[i] >= n)
+            return "import: a level-0 link points outside the graph";
+    for (size_t i = 0; i < upper * (size_t)m; ++i)
+        if (new_adju[i] != kEmpty && new_adju[i] >= n)
+            return "import: an upper-level link points outside the graph";
+    // everything checked: only now is the old graph dropped
+    const uint32_t keep_m = m, keep_m0 = m0, keep_ef_add = ef_add, keep_ef_search = ef_search, keep_vb = vec_bytes;
+    const uint64_t keep_ndim = ndim;
+    reset_graph();
+    m = keep_m, m0 = keep_m0, ef_add = keep_ef_add, ef_search = keep_ef_search, vec_bytes = keep_vb, ndim = keep_ndim;
+    keys.assign(new_keys, new_keys + n);
+    levels.assign(new_levels, new_levels + n);
+    upper_off.assign(n + 1, 0);
+    for (size_t i = 0; i < n; ++i)
+        upper_off[i + 1] = upper_off[i] + (uint64_t)levels[i];
+    adj0.assign(new_adj0, new_adj0 + n * (size_t)m0);
+    adju.assign(new_adju, new_adju + upper * (size_t)m);
+    if (vectors && n)
+        host_vectors.assign(vectors, vectors + n * (size_t)vec_bytes);
+    vectors_excluded = vectors == nullptr;
+    max_level = top;
+    entry = new_entry;
+    capacity = n;
+    std::vector<int16_t> scratch;
+    level_rng = 1;
+    draw_levels(n, scratch);  // further insertions continue the single stream
+    keys_ascending_ = true;
+    max_key_ = 0;
+    for (size_t i = 0; i < n; ++i) {
+        if (i && keys[i] <= max_key_)
+            keys_ascending_ = false;
+        max_key_ = std::max(max_key_, keys[i]);
+    }
+    rebuild_level_index();
+    return {};
+}
+
 // ------------------------------------------------------------------------------------------------ accessors
 static inline size_t node_bytes(uint32_t m, uint32_t m0, int level) {
     return 10 + 4 * (1 + (size_t)m0) + (size_t)level * 4 * (1 + (size_t)m);

@@ -85,6 +85,12 @@ class HostIndex {
 
     // draws the levels of the next `n` nodes from the single reference stream
     void draw_levels(size_t n, std::vector<int16_t>& out);
+    // an EMPTY index whose first node will be row `first_row` of the single stream: a row shard of a larger build
+    // draws exactly the levels a one-piece build gives those rows
+    void seek_level_stream(uint64_t first_row);
+    // replace the graph by one assembled elsewhere (the cross-shard stitch): arrays in this class's layout
+    std::string import_graph(uint64_t const* new_keys, int16_t const* new_levels, uint32_t const* new_adj0,
+                             uint32_t const* new_adju, uint8_t const* vectors, size_t n, uint64_t new_entry);
 
     uint64_t key_of(size_t slot) const;
     int level_of(size_t slot) const;

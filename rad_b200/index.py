@@ -199,6 +199,7 @@ class Index:
         bloom_bits_log2: int = 0,
         _debug_max_batches: int = 0,
         _no_batch_tile: bool = False,
+        _connectivity_base: int = 0,
     ) -> None:
         if connectivity is None:
             connectivity = DEFAULT_CONNECTIVITY
@@ -223,7 +224,9 @@ class Index:
             flags=(_native.RB_FLAG_LAZY_HOST_SYNC if lazy_host_sync else 0)
             | (_native.RB_FLAG_TIME_KERNELS if time_kernels else 0),
             batch_growth_den=batch_growth_den, batch_max=batch_max, bloom_bits_log2=bloom_bits_log2,
-            debug_max_batches=_debug_max_batches, no_batch_tile=1 if _no_batch_tile else 0)
+            debug_max_batches=_debug_max_batches, no_batch_tile=1 if _no_batch_tile else 0,
+            connectivity_base=_connectivity_base)
+        self._connectivity_base = int(_connectivity_base)
         err = C.c_char_p()
         self._lib = _native.lib()
         self._h = self._lib.rb_init(C.byref(opts), C.byref(err))
@@ -577,11 +580,58 @@ class Index:
         self._lib.rb_release_device(self._handle(), 1 if keep_host_vectors else 0, C.byref(err))
         self._check(err)
 
+    # ------------------------------------------------------------------ pieces of the cross-shard stitch (sharded.py)
+    def seek_level_stream(self, first_row: int) -> None:
+        """This EMPTY index is the shard starting at global row ``first_row``: its nodes draw the levels a one-piece
+        build gives those rows (the reference's single level stream, index.hpp:3867-3871)."""
+        err = C.c_char_p()
+        self._lib.rb_seek_level_stream(self._handle(), int(first_row), C.byref(err))
+        self._check(err)
+
+    def add_device(self, keys, d_vectors_ptr: int, count: int, levels=None) -> None:
+        """Insert ``count`` fingerprints that are already in HBM (``d_vectors_ptr``: device address of count x 128
+        bytes).  ``levels`` (int16 per row) prescribes the levels instead of drawing them from the level stream."""
+        err = C.c_char_p()
+        kptr = None
+        if keys is not None:
+            keys = np.ascontiguousarray(keys, dtype=np.uint64)
+            kptr = keys.ctypes.data
+        if levels is None:
+            self._lib.rb_add_device(self._handle(), kptr, d_vectors_ptr, int(count), C.byref(err))
+        else:
+            levels = np.ascontiguousarray(levels, dtype=np.int16)
+            assert len(levels) == count
+            self._lib.rb_add_device_levels(self._handle(), kptr, d_vectors_ptr, int(count), levels.ctypes.data,
+                                           C.byref(err))
+        self._check(err)
+
+    def import_graph(self, keys, levels, adj0, adj_upper, vectors, entry: int) -> None:
+        """Replace the graph by one assembled elsewhere (global slots): see ``rb_import_graph``."""
+        keys = np.ascontiguousarray(keys, dtype=np.uint64)
+        levels = np.ascontiguousarray(levels, dtype=np.int16)
+        n = len(keys)
+        adj0 = np.ascontiguousarray(adj0, dtype=np.uint32).reshape(n, -1)
+        adj_upper = np.ascontiguousarray(adj_upper, dtype=np.uint32).reshape(-1, self.connectivity)
+        assert adj0.shape[1] == self.connectivity_base and len(adj_upper) == int(levels.astype(np.int64).sum())
+        vptr = None
+        if vectors is not None:
+            vectors = np.ascontiguousarray(vectors, dtype=np.uint8).reshape(n, -1)
+            assert vectors.shape[1] == self.ndim // 8
+            vptr = vectors.ctypes.data
+        err = C.c_char_p()
+        self._lib.rb_import_graph(self._handle(), keys.ctypes.data, levels.ctypes.data, adj0.ctypes.data,
+                                  adj_upper.ctypes.data if len(adj_upper) else None, vptr, n, int(entry), C.byref(err))
+        self._check(err)
+
+    @property
+    def connectivity_base(self) -> int:
+        return self._connectivity_base or 2 * self.connectivity
+
     def _debug_adjacency(self):
         """(adj0 [n, 2M], adj_upper [rows, M]) with 0xFFFFFFFF padding -- tests compare these with the CPU model."""
         n, m = len(self), self.connectivity
         rows = int(self._lib.rb_debug_adjacency(self._handle(), None, None))
-        adj0 = np.empty((n, 2 * m), dtype=np.uint32)
+        adj0 = np.empty((n, self.connectivity_base), dtype=np.uint32)
         adju = np.empty((rows, m), dtype=np.uint32)
         self._lib.rb_debug_adjacency(self._handle(), adj0.ctypes.data, adju.ctypes.data if rows else None)
         return adj0, adju

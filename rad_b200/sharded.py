@@ -175,3 +175,305 @@ class ShardedIndex:
         return BatchMatches(keys=out_keys, distances=out_d, counts=out_c,
                             visited_members=int(getattr(got, "visited_members", 0)),
                             computed_distances=int(getattr(got, "computed_distances", 0)))
+
+
+# ================================================================================================ one graph from G shards
+EMPTY_SLOT = -1  # 0xFFFFFFFF in the int32 tensors that carry u32 slots between torch and the C ABI
+
+
+def stitch_parameters(world: int) -> Tuple[int, int]:
+    """(remote candidates per node and shard, ef of the remote searches): with few shards every other shard matters
+    (half of a node's true neighbours live there), with many the union of their answers does (measured with
+    scripts/stitch_probe.py: recall of the stitched graph within 0.5 points of the one-piece graph at 2..8 shards)."""
+    return (16, 128) if world <= 3 else (8, 64)
+
+
+class DeviceShard:
+    """The C-ABI calls the stitch needs from one rank's sub-index, on torch CUDA tensors (``rb_copy_vectors_device``,
+    ``rb_search_device``, ``rb_gather_vectors_device``, ``rb_stitch_device``)."""
+
+    def __init__(self, index, device=None):
+        import torch
+        from . import _native
+        self._torch, self._native, self.index = torch, _native, index
+        self._lib = _native.lib()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.m, self.m0 = index.connectivity, index.connectivity_base
+
+    def __len__(self):
+        return len(self.index)
+
+    def _settle(self):
+        """The library works on the handle's own (non-blocking) stream and returns when its work is done; what torch
+        queued on ITS stream -- the tensors handed in -- must be complete before the library reads them."""
+        self._torch.cuda.current_stream(self.device).synchronize()
+
+    def levels(self) -> np.ndarray:
+        return self.index.levels
+
+    def vectors(self, first: int, count: int, out):
+        self._settle()
+        err = C.c_char_p()
+        self._lib.rb_copy_vectors_device(self.index._handle(), first, count, out.data_ptr(), C.byref(err))
+        self._native.check(err)
+
+    def gather_vectors(self, slots):
+        torch = self._torch
+        out = torch.empty((slots.numel(), 128), dtype=torch.uint8, device=self.device)
+        self._settle()
+        err = C.c_char_p()
+        self._lib.rb_gather_vectors_device(self.index._handle(), slots.data_ptr(), slots.numel(), out.data_ptr(),
+                                           C.byref(err))
+        self._native.check(err)
+        return out
+
+    def remote_candidates(self, queries, k: int, ef: int):
+        """The k nearest rows of THIS shard for foreign queries -> (local slots int32 [n, k], EMPTY_SLOT = none;
+        their fingerprints uint8 [n, k, 128])."""
+        torch = self._torch
+        n = int(queries.shape[0])
+        slots = torch.full((n, k), EMPTY_SLOT, dtype=torch.int32, device=self.device)
+        dists = torch.empty((n, k), dtype=torch.float32, device=self.device)
+        counts = torch.zeros((n,), dtype=torch.int32, device=self.device)
+        if n and len(self.index):
+            self.index.expansion_search = ef
+            self._settle()
+            err = C.c_char_p()
+            self._lib.rb_search_device(self.index._handle(), queries.data_ptr(), n, k, 0, slots.data_ptr(),
+                                       dists.data_ptr(), counts.data_ptr(), C.byref(err))
+            self._native.check(err)
+            slots = torch.where(torch.arange(k, device=self.device)[None, :] < counts[:, None], slots,
+                                torch.full_like(slots, EMPTY_SLOT))
+        return slots, self.gather_vectors(slots.reshape(-1).contiguous()).reshape(n, k, 128)
+
+    def stitch(self, first: int, count: int, slot_base: int, cand_slots, cand_fp, out_rows):
+        self._settle()
+        err = C.c_char_p()
+        self._lib.rb_stitch_device(self.index._handle(), first, count, slot_base, cand_slots.data_ptr(),
+                                   cand_fp.data_ptr(), int(cand_slots.shape[1]), out_rows.data_ptr(), C.byref(err))
+        self._native.check(err)
+
+    def build_upper(self, fingerprints, levels_minus_one: np.ndarray, expansion_add: int):
+        """A fresh build over the gathered upper-level nodes, one level down, level-0 rows M wide ->
+        (adj0 [n, M], adj_upper, entry, max_level) of that build."""
+        from .index import Index
+        up = Index(ndim=self.index.ndim, connectivity=self.m, expansion_add=expansion_add,
+                   device=self.device.index if self.device.index is not None else -1, _connectivity_base=self.m)
+        fp = fingerprints.to(self.device).contiguous()
+        self._settle()
+        up.add_device(None, fp.data_ptr(), len(levels_minus_one), levels=levels_minus_one)
+        a0, au = up._debug_adjacency()
+        return a0, au, up.entry_slot, up.max_level
+
+
+class TorchComm:
+    """The collectives of the stitch over ``torch.distributed`` (NCCL between GPUs, gloo in the CPU tests)."""
+
+    def __init__(self):
+        import torch.distributed as dist
+        self._dist = dist if dist.is_available() and dist.is_initialized() else None
+        self.world = self._dist.get_world_size() if self._dist else 1
+        self.rank = self._dist.get_rank() if self._dist else 0
+
+    def all_gather(self, t):
+        import torch
+        if self.world == 1:
+            return t.unsqueeze(0)
+        out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
+        self._dist.all_gather_into_tensor(out.view(-1), t.contiguous().view(-1))
+        return out
+
+    def all_to_all(self, send):
+        """send[h] goes to rank h; returns recv with recv[h] = what rank h sent here"""
+        import torch
+        send = send.contiguous()
+        recv = torch.empty_like(send)
+        self._dist.all_to_all_single(recv.view(-1), send.view(-1))
+        return recv
+
+    def gather0(self, t):
+        import torch
+        if self.world == 1:
+            return [t]
+        out = [torch.empty_like(t) for _ in range(self.world)] if self.rank == 0 else None
+        self._dist.gather(t.contiguous(), out, dst=0)
+        return out
+
+    def barrier(self):
+        if self._dist is not None:
+            self._dist.barrier()
+
+
+class LocalComm:
+    """The same collectives between THREADS of one process: several shards (handles) on one GPU, as the single-GPU
+    tests run the stitch.  ``LocalComm(world).rank_view(r)`` is rank r's end."""
+
+    def __init__(self, world: int):
+        import threading
+        self.world = world
+        self._box = [None] * world
+        self._bar = threading.Barrier(world)
+
+    def rank_view(self, rank: int):
+        return _LocalRank(self, rank)
+
+
+class _LocalRank:
+    def __init__(self, hub: LocalComm, rank: int):
+        self._hub, self.rank, self.world = hub, rank, hub.world
+
+    def _exchange(self, t):
+        self._hub._box[self.rank] = t
+        self._hub._bar.wait()
+        got = list(self._hub._box)
+        self._hub._bar.wait()
+        return got
+
+    def all_gather(self, t):
+        import torch
+        return torch.stack(self._exchange(t))
+
+    def all_to_all(self, send):
+        import torch
+        return torch.stack([part[self.rank] for part in self._exchange(send)])
+
+    def gather0(self, t):
+        got = self._exchange(t)
+        return got if self.rank == 0 else None
+
+    def barrier(self):
+        self._hub._bar.wait()
+
+
+def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 65536,
+                       k_remote: int | None = None, ef_merge: int | None = None, timings: dict | None = None,
+                       comm=None):
+    """ONE HNSW graph with global slots from the sub-graphs every rank built over its own row shard (SURVEY.md §8e
+    row 3).  Collective: every rank calls it with its ``DeviceShard`` and the global slot of its first row; shards
+    are contiguous and ordered by rank.
+
+    1. STITCH, level 0, in rounds of ``batch`` nodes per rank: all-gather of the round's fingerprints (NCCL); every rank
+       answers the other ranks' rows from its own graph (``k_remote`` nearest at ef ``ef_merge``) and sends the answers
+       WITH their fingerprints back (all-to-all); every rank prunes own links + remote candidates with the reference's
+       heuristic into rows of global slots (``rb_stitch_device``).  The sub-graphs themselves stay untouched.
+    2. UPPER LEVELS: the nodes with level >= 1 (1/M of all) are gathered on rank 0 and built there as one graph, one
+       level down; its rows, mapped back to global slots, are levels 1.. of the global graph.
+    Returns on rank 0 ``dict(levels, adj0, adj_upper, entry, max_level)`` (host arrays, global slots) after gathering
+    the stitched rows; ``None`` on the other ranks."""
+    import time
+
+    import torch
+    comm = TorchComm() if comm is None else comm
+    world, rank = comm.world, comm.rank
+    all_gather, gather0 = comm.all_gather, comm.gather0
+    dev = shard.device
+    kr, efm = stitch_parameters(world)
+    kr = k_remote or kr
+    efm = ef_merge or efm
+    n_local, m, m0 = len(shard), shard.m, shard.m0
+    t_start = time.perf_counter()
+
+    def sync():
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+
+    sizes = all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).view(-1).tolist()
+    bases = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    assert int(bases[rank]) == int(slot_base), "shards must be contiguous and ordered by rank"
+    rows_global = torch.full((n_local, m0), EMPTY_SLOT, dtype=torch.int32, device=dev)
+    others = [h for h in range(world) if h != rank]
+    # ---- 1. stitch
+    for r0 in range(0, max(sizes), batch):
+        cnt = max(0, min(batch, n_local - r0))
+        q = torch.zeros((batch, 128), dtype=torch.uint8, device=dev)
+        if cnt:
+            shard.vectors(r0, cnt, q)
+        if world == 1:
+            cand_slots = torch.full((cnt, 0), EMPTY_SLOT, dtype=torch.int32, device=dev)
+            cand_fp = torch.zeros((cnt, 0, 128), dtype=torch.uint8, device=dev)
+        else:
+            allq = all_gather(q)                                            # [world, batch, 128]
+            counts = [max(0, min(batch, sizes[h] - r0)) for h in range(world)]
+            send_slots = torch.full((world, batch, kr), EMPTY_SLOT, dtype=torch.int32, device=dev)
+            send_fp = torch.zeros((world, batch, kr, 128), dtype=torch.uint8, device=dev)
+            for src in others:
+                if not counts[src]:
+                    continue
+                s, f = shard.remote_candidates(allq[src, :counts[src]].contiguous(), kr, efm)
+                send_slots[src, :counts[src]] = torch.where(s != EMPTY_SLOT, s + int(slot_base), s)  # global slots
+                send_fp[src, :counts[src]] = f
+            sync()
+            recv_slots, recv_fp = comm.all_to_all(send_slots), comm.all_to_all(send_fp)
+            # recv[h] = what shard h found for MY rows; own block dropped
+            cand_slots = recv_slots[others].permute(1, 0, 2).reshape(batch, len(others) * kr)[:cnt].contiguous()
+            cand_fp = recv_fp[others].permute(1, 0, 2, 3).reshape(batch, len(others) * kr, 128)[:cnt].contiguous()
+        if cnt:
+            shard.stitch(r0, cnt, int(slot_base), cand_slots, cand_fp, rows_global[r0:r0 + cnt])
+    sync()
+    comm.barrier()
+    t_stitch = time.perf_counter()
+    # ---- 2. upper levels on rank 0
+    lv = np.asarray(shard.levels(), dtype=np.int16)
+    up_local = np.flatnonzero(lv >= 1).astype(np.int64)
+    n_up = all_gather(torch.tensor([len(up_local)], dtype=torch.int64, device=dev)).view(-1).tolist()
+    cap = max(max(n_up), 1)
+    up_slots = torch.full((cap,), EMPTY_SLOT, dtype=torch.int32, device=dev)
+    up_fp = torch.zeros((cap, 128), dtype=torch.uint8, device=dev)
+    up_lv = torch.zeros((cap,), dtype=torch.int16, device=dev)
+    if len(up_local):
+        idx = torch.from_numpy(up_local.astype(np.int32)).to(dev)
+        up_slots[:len(up_local)] = idx
+        up_fp[:len(up_local)] = shard.gather_vectors(idx)
+        up_lv[:len(up_local)] = torch.from_numpy(lv[up_local]).to(dev)
+    g_slots, g_fp, g_lv = gather0(up_slots), gather0(up_fp), gather0(up_lv)
+    # the stitched level-0 rows and the levels, padded to the largest shard, to rank 0
+    pad = max(sizes)
+    rows_pad = rows_global
+    if n_local < pad:
+        rows_pad = torch.cat([rows_global, torch.full((pad - n_local, m0), EMPTY_SLOT, dtype=torch.int32, device=dev)])
+    g_rows = gather0(rows_pad)
+    lv_pad = torch.zeros((pad,), dtype=torch.int16, device=dev)
+    lv_pad[:n_local] = torch.from_numpy(lv).to(dev)
+    g_levels = gather0(lv_pad)
+    result = None
+    if rank == 0:
+        result = _assemble_global(shard, world, sizes, bases, n_up, g_slots, g_fp, g_lv, g_rows, g_levels, m,
+                                  expansion_add)
+    sync()
+    comm.barrier()
+    if timings is not None:
+        timings["stitch_s"] = t_stitch - t_start
+        timings["upper_and_gather_s"] = time.perf_counter() - t_stitch
+        timings["k_remote"], timings["ef_merge"] = kr, efm
+    return result
+
+
+def _assemble_global(shard, world, sizes, bases, n_up, g_slots, g_fp, g_lv, g_rows, g_levels, m, expansion_add):
+    """Rank 0: the gathered pieces -> host arrays of the global graph; the upper levels are built here."""
+    import torch
+    n_total = int(bases[-1])
+    levels = np.concatenate([g_levels[h][:sizes[h]].cpu().numpy() for h in range(world)]).astype(np.int16)
+    adj0 = np.concatenate([g_rows[h][:sizes[h]].cpu().numpy() for h in range(world)]).view(np.uint32)
+    up_global = np.concatenate([g_slots[h][:n_up[h]].cpu().numpy().astype(np.int64) + bases[h] for h in range(world)])
+    up_levels = np.concatenate([g_lv[h][:n_up[h]].cpu().numpy() for h in range(world)]).astype(np.int16)
+    upper_off = np.concatenate([[0], np.cumsum(levels.astype(np.int64))])
+    adj_upper = np.full((int(upper_off[-1]), m), 0xFFFFFFFF, dtype=np.uint32)
+    entry, max_level = 0, int(levels.max()) if n_total else 0
+    if len(up_global):
+        fp_all = torch.cat([g_fp[h][:n_up[h]].to(shard.device) for h in range(world)])
+        a0, au, sub_entry, sub_max = shard.build_upper(fp_all, (up_levels - 1).astype(np.int16), expansion_add)
+        table = np.append(up_global, 0xFFFFFFFF).astype(np.uint32)  # sub slot -> global slot, EMPTY -> EMPTY
+
+        def to_global(rows):
+            return table[np.where(rows == 0xFFFFFFFF, len(up_global), rows).astype(np.int64)]
+
+        first_row = upper_off[up_global]  # the level-1 row of every upper node
+        adj_upper[first_row] = to_global(a0)
+        if len(au):
+            sub_off = np.concatenate([[0], np.cumsum((up_levels - 1).astype(np.int64))])
+            owner = np.repeat(np.arange(len(up_global)), (up_levels - 1).astype(np.int64))
+            rel = np.arange(len(au)) - sub_off[owner]  # 0 = level 2 of the graph
+            adj_upper[first_row[owner] + 1 + rel] = to_global(au)
+        entry = int(up_global[sub_entry])
+        assert max_level == sub_max + 1
+    return dict(levels=levels, adj0=adj0, adj_upper=adj_upper, entry=entry, max_level=max_level)

@@ -631,3 +631,40 @@ BM_EXPORT void bm_counters(const bm_index* ix, uint64_t* out2) {
     out2[0] = ix->computed_distances;
     out2[1] = ix->expansions;
 }
+
+/* The cross-shard stitch of one level-0 row (rad_b200/csrc: stitch_kernel): candidates = the node's own links and the
+ * remote shards' answers (global slots, EMPTY padded, duplicates allowed), ordered by (distance, slot) and pruned by
+ * the same heuristic as everything else, needed = row width.  vecs holds ALL rows (global slots). */
+BM_EXPORT void bm_stitch_rows(const uint8_t* vecs, uint64_t nq, const uint32_t* qslots, const uint32_t* cands,
+                              uint32_t ncand, uint32_t needed, uint32_t* out) {
+    bm_index fake;
+    memset(&fake, 0, sizeof(fake));
+    fake.vecs = vecs;
+#pragma omp parallel
+    {
+        uint64_t* keys = (uint64_t*)malloc((size_t)ncand * 8);
+        uint64_t* sel = (uint64_t*)malloc((size_t)(ncand + 1) * 8);
+        uint64_t nd = 0;
+#pragma omp for schedule(dynamic, 64)
+        for (uint64_t r = 0; r < nq; ++r) {
+            const uint8_t* q = vecs + (size_t)qslots[r] * 128;
+            uint32_t nk = 0;
+            for (uint32_t j = 0; j < ncand; ++j) {
+                uint32_t c = cands[r * ncand + j];
+                if (c == EMPTY || c == qslots[r])
+                    continue;
+                keys[nk++] = ((uint64_t)dist_bits(q, vecs + (size_t)c * 128) << 32) | c;
+            }
+            qsort(keys, nk, 8, u64_cmp);
+            uint32_t uniq = 0;
+            for (uint32_t j = 0; j < nk; ++j)
+                if (!uniq || keys[j] != keys[uniq - 1])
+                    keys[uniq++] = keys[j];
+            uint32_t ns = select_neighbors(&fake, keys, uniq, needed, sel, &nd);
+            for (uint32_t j = 0; j < needed; ++j)
+                out[r * needed + j] = j < ns ? (uint32_t)sel[j] : EMPTY;
+        }
+        free(keys);
+        free(sel);
+    }
+}

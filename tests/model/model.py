@@ -40,6 +40,7 @@ def lib() -> C.CDLL:
             getattr(L, name).restype = rt
             getattr(L, name).argtypes = [C.c_void_p]
         L.bm_counters.argtypes = [C.c_void_p, _u64p]
+        L.bm_stitch_rows.argtypes = [_u8p, C.c_uint64, _u32p, _u32p, C.c_uint32, C.c_uint32, _u32p]
         _LIB = L
     return _LIB
 
@@ -150,3 +151,13 @@ def write_usearch(path, vecs, keys, levels, adj0, adju, m, max_level, entry, ndi
         f.write(np.array([n, m, m0, max_level, entry], dtype=np.uint64).tobytes())
         f.write(levels.tobytes())
         f.write(tape.tobytes())
+
+
+def stitch_rows(vecs, qslots, cands, needed):
+    """heuristic over (own links + remote candidates) per node -> uint32 [n, needed] (batched_model.c: bm_stitch_rows)"""
+    vecs = np.ascontiguousarray(vecs, dtype=np.uint8)
+    qslots = np.ascontiguousarray(qslots, dtype=np.uint32)
+    cands = np.ascontiguousarray(cands, dtype=np.uint32)
+    out = np.empty((len(qslots), needed), dtype=np.uint32)
+    lib().bm_stitch_rows(vecs, len(qslots), qslots, cands, cands.shape[1], needed, out)
+    return out

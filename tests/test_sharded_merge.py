@@ -128,3 +128,43 @@ def test_sharded_index_search_equals_unsharded(tmp_path, n, nq, k):
         c = int(counts[r])
         assert np.array_equal(a["keys"][r, :c], slots[r, :c].astype(np.uint64) + np.uint64(1000))
         assert np.array_equal(a["distances"][r, :c].view(np.uint32), dists[r, :c].view(np.uint32))
+
+
+def _comm_worker(rank, world, port, out):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from rad_b200.sharded import TorchComm
+        comm = TorchComm()
+        g = comm.all_gather(torch.tensor([rank * 10, rank * 10 + 1]))
+        send = torch.stack([torch.tensor([100 * rank + h, 100 * rank + h + 50]) for h in range(world)])
+        recv = comm.all_to_all(send)
+        got0 = comm.gather0(torch.tensor([rank + 7]))
+        comm.barrier()
+        out.put((rank, g.tolist(), recv.tolist(), None if got0 is None else [t.tolist() for t in got0]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_stitch_collectives_over_gloo():
+    """TorchComm (what the stitch uses between the ranks) against the semantics LocalComm gives the single-GPU tests:
+    all_gather stacks by rank, all_to_all delivers send[h] to rank h, gather0 collects on rank 0."""
+    import multiprocessing as pymp
+    world = 2
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = pymp.get_context("spawn")
+    out = ctx.Queue()
+    procs = [ctx.Process(target=_comm_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = sorted(out.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(30)
+    for rank, g, recv, g0 in got:
+        assert g == [[0, 1], [10, 11]]
+        assert recv == [[100 * h + rank, 100 * h + rank + 50] for h in range(world)]
+        assert g0 == ([[7], [8]] if rank == 0 else None)
