@@ -141,6 +141,19 @@ RB_EXPORT void rb_exact_topk_device(void const* d_database, uint64_t rows, uint6
 RB_EXPORT size_t rb_exact_topk_workspace_bytes(uint64_t rows, uint64_t query_count, uint32_t k);
 /* k-way merge of `parts` partial results [parts x Q x k] (e.g. the all-gathered per-shard keys; the merge rule of
  * index.hpp:2625-2645) into d_keys_out [Q x k]. */
+/* rb_exact_topk_device for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same inputs, same
+ * d_keys_out, bit-identical results; the workspace is a file-scope static device array of RB_NOALLOC_SCRATCH_BYTES
+ * (16 MiB, held by every GPU that loads the library until the process exits), so the call makes no cudaMalloc /
+ * cudaFree and uses no allocating library routine.  A search whose workspace (rb_exact_topk_workspace_bytes) exceeds
+ * the array is REJECTED with an error naming both sizes.  All calls on one GPU share the array: calls that overlap on
+ * the GPU (different streams) race -- serialise them.  The array keeps the last call's contents; every call
+ * re-initialises what it reads.  The device of `stream` must be current. */
+#define RB_NOALLOC_SCRATCH_BYTES (16u << 20)
+RB_EXPORT size_t rb_exact_topk_noalloc_max_bytes(void);
+RB_EXPORT void rb_exact_topk_device_noalloc(void const* d_database, uint64_t rows, uint64_t slot_base,
+                                            void const* d_queries, uint64_t query_count, uint32_t k, void* d_keys_out,
+                                            uintptr_t stream, rb_error_t* error);
 RB_EXPORT void rb_merge_topk_device(void const* d_partial_keys, uint32_t parts, uint64_t query_count, uint32_t k,
                                     void* d_keys_out, uintptr_t stream, rb_error_t* error);
 /* split merged keys into slots (u64), distances (f32) and counts (i64) -- all device pointers */

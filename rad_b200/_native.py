@@ -80,6 +80,9 @@ SIGNATURES = {
     "rb_exact_topk_device": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_uint32,
                                     C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, _ERR]),
     "rb_exact_topk_workspace_bytes": (C.c_size_t, [C.c_uint64, C.c_uint64, C.c_uint32]),
+    "rb_exact_topk_noalloc_max_bytes": (C.c_size_t, []),
+    "rb_exact_topk_device_noalloc": (None, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_uint32,
+                                            C.c_void_p, C.c_size_t, _ERR]),
     "rb_merge_topk_device": (None, [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p, C.c_size_t, _ERR]),
     "rb_unpack_topk_device": (None, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_size_t, _ERR]),

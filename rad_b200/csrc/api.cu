@@ -1150,7 +1150,7 @@ ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
 
 std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uint4 const* queries, uint64_t nq,
                          uint32_t k, uint64_t* keys_out, void* workspace, size_t workspace_bytes,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, bool allow_debug_counters = true) {
     if (!nq)
         return {};
     if (k == 0 || k > 1024)
@@ -1183,7 +1183,7 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
         ep.bounds = nullptr;
     ep.debug_cycles = nullptr;
     static unsigned long long* dbg_dev = nullptr;
-    if (pl.tensor && std::getenv("RB_EXACT_DEBUG")) {
+    if (allow_debug_counters && pl.tensor && std::getenv("RB_EXACT_DEBUG")) {  // (this aid allocates its counters)
         if (!dbg_dev)
             RB_CUDA(cudaMalloc(&dbg_dev, 32 * sizeof(unsigned long long)));
         RB_CUDA(cudaMemsetAsync(dbg_dev, 0, 32 * sizeof(unsigned long long), stream));
@@ -1726,6 +1726,66 @@ void rb_exact_topk_device(void const* d_database, uint64_t rows, uint64_t slot_b
                                    static_cast<uint4 const*>(d_queries), query_count, k,
                                    static_cast<uint64_t*>(d_keys_out), d_workspace, workspace_bytes,
                                    reinterpret_cast<cudaStream_t>(stream));
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
+}  // extern "C"
+
+// ---- rb_exact_topk_device_noalloc: the workspace of the exact search in a STATIC device array (see include/rad_b200.h).
+// Every GPU that loads the library holds these RB_NOALLOC_SCRATCH_BYTES until the process exits.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RB_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is asked for
+// once per device, with that device current, and cached.
+std::string noalloc_scratch_address(void*& out) {
+    static std::mutex mu;
+    static void* address[64] = {nullptr};
+    int dev = 0;
+    RB_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64)
+        return "rb_exact_topk_device_noalloc supports device ordinals below 64";
+    std::lock_guard<std::mutex> lock(mu);
+    if (!address[dev]) {
+        void* ptr = nullptr;
+        RB_CUDA(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        address[dev] = ptr;
+    }
+    out = address[dev];
+    return {};
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t rb_exact_topk_noalloc_max_bytes(void) { return RB_NOALLOC_SCRATCH_BYTES; }
+
+void rb_exact_topk_device_noalloc(void const* d_database, uint64_t rows, uint64_t slot_base, void const* d_queries,
+                                  uint64_t query_count, uint32_t k, void* d_keys_out, uintptr_t stream,
+                                  rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!query_count)
+        return;
+    if (k == 0 || k > 1024)
+        RB_FAIL("k must be in 1..1024");
+    const ExactPlan pl = plan_exact(rows, query_count, k);
+    const size_t need = pl.keys_bytes + pl.iu_bytes;
+    if (need > (size_t)RB_NOALLOC_SCRATCH_BYTES)
+        RB_FAIL(format("rb_exact_topk_device_noalloc: this search needs %zu bytes of scratch, the static array holds %zu "
+                       "(fewer queries per call or a smaller k; or rb_exact_topk_device with a caller workspace)",
+                       need, (size_t)RB_NOALLOC_SCRATCH_BYTES));
+    void* scratch = nullptr;
+    std::string err = noalloc_scratch_address(scratch);
+    // the kernels initialise every list of the workspace they use and launch_exact resets the bound words, so the
+    // contents the previous call left behind are never read
+    if (err.empty())
+        err = launch_exact(static_cast<uint4 const*>(d_database), rows, slot_base, static_cast<uint4 const*>(d_queries),
+                           query_count, k, static_cast<uint64_t*>(d_keys_out), scratch, need,
+                           reinterpret_cast<cudaStream_t>(stream), /*allow_debug_counters=*/false);
     if (!err.empty())
         RB_FAIL(err);
 }
