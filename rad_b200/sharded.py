@@ -128,6 +128,47 @@ class ShardedIndex:
         dist = torch.distributed
         self._dist = dist if dist.is_available() and dist.is_initialized() else None
         self.world = self._dist.get_world_size() if self._dist else 1
+        if len(local_index) == 0 and hasattr(local_index, "seek_level_stream"):
+            # the shard draws ITS rows of the reference's single level stream: the global graph gets the levels of a
+            # one-piece build (index.hpp:3867-3871)
+            local_index.seek_level_stream(self.slot_base)
+
+    def build_global(self, *, with_vectors: bool = True, expansion_add: int | None = None, timings: dict | None = None):
+        """ONE graph over all shards (``build_global_graph``: cross-shard stitch + upper levels on rank 0).  Collective.
+        Returns on rank 0 a ``rad_b200.index.Index`` holding the global graph in global slots with the users' keys --
+        ``save(path)`` writes the single `.usearch` file RAD serves (scripts/start_hnsw_server.py:69) -- and ``None``
+        on the other ranks.  ``with_vectors=False`` leaves the fingerprints on their GPUs (a file for
+        ``Index(path, view=True, exclude_vectors=True)``)."""
+        import torch
+        from .index import Index
+        shard = DeviceShard(self.local)
+        comm = TorchComm()
+        ef_add = int(expansion_add or self.local.expansion_add)
+        res = build_global_graph(shard, self.slot_base, expansion_add=ef_add, timings=timings, comm=comm)
+        n_local = len(self.local)
+        sizes = comm.all_gather(torch.tensor([n_local], dtype=torch.int64, device=shard.device)).view(-1).tolist()
+        pad = max(sizes)
+        keys = torch.zeros((pad,), dtype=torch.int64, device=shard.device)
+        keys[:n_local] = torch.from_numpy(np.asarray(self.local.keys, dtype=np.uint64).view(np.int64)).to(shard.device)
+        g_keys = comm.gather0(keys)
+        g_fp = None
+        if with_vectors:
+            fp = torch.zeros((pad, 128), dtype=torch.uint8, device=shard.device)
+            if n_local:
+                shard.vectors(0, n_local, fp)
+            g_fp = comm.gather0(fp)
+        if comm.rank != 0:
+            return None
+        all_keys = np.concatenate([g_keys[h][:sizes[h]].cpu().numpy() for h in range(comm.world)]).view(np.uint64)
+        vectors = None
+        if with_vectors:
+            vb = self.local.ndim // 8
+            vectors = np.concatenate([g_fp[h][:sizes[h], :vb].cpu().numpy() for h in range(comm.world)])
+        whole = Index(ndim=self.local.ndim, connectivity=self.local.connectivity, expansion_add=ef_add,
+                      expansion_search=self.local.expansion_search,
+                      device=shard.device.index if shard.device.index is not None else -1, exclude_vectors=not with_vectors)
+        whole.import_graph(all_keys, res["levels"], res["adj0"], res["adj_upper"], vectors, res["entry"])
+        return whole
 
     def __len__(self) -> int:
         n = len(self.local)
@@ -347,7 +388,7 @@ class _LocalRank:
 
 def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 65536,
                        k_remote: int | None = None, ef_merge: int | None = None, timings: dict | None = None,
-                       comm=None):
+                       comm=None, assemble: bool = True):
     """ONE HNSW graph with global slots from the sub-graphs every rank built over its own row shard (SURVEY.md §8e
     row 3).  Collective: every rank calls it with its ``DeviceShard`` and the global slot of its first row; shards
     are contiguous and ordered by rank.
@@ -359,7 +400,9 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
     2. UPPER LEVELS: the nodes with level >= 1 (1/M of all) are gathered on rank 0 and built there as one graph, one
        level down; its rows, mapped back to global slots, are levels 1.. of the global graph.
     Returns on rank 0 ``dict(levels, adj0, adj_upper, entry, max_level)`` (host arrays, global slots) after gathering
-    the stitched rows; ``None`` on the other ranks."""
+    the stitched rows; ``None`` on the other ranks.  With ``assemble=False`` the stitched level-0 rows STAY on their
+    GPUs: every rank gets ``dict(rows=int32 cuda tensor [n_local, 2M] of global slots)`` and rank 0's dict also holds
+    ``levels, adj_upper, entry, max_level`` -- the device-resident result ``bench.py`` times."""
     import time
 
     import torch
@@ -426,12 +469,15 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
         up_fp[:len(up_local)] = shard.gather_vectors(idx)
         up_lv[:len(up_local)] = torch.from_numpy(lv[up_local]).to(dev)
     g_slots, g_fp, g_lv = gather0(up_slots), gather0(up_fp), gather0(up_lv)
-    # the stitched level-0 rows and the levels, padded to the largest shard, to rank 0
+    # the levels and (when assembling) the stitched level-0 rows, padded to the largest shard, to rank 0
     pad = max(sizes)
-    rows_pad = rows_global
-    if n_local < pad:
-        rows_pad = torch.cat([rows_global, torch.full((pad - n_local, m0), EMPTY_SLOT, dtype=torch.int32, device=dev)])
-    g_rows = gather0(rows_pad)
+    g_rows = None
+    if assemble:
+        rows_pad = rows_global
+        if n_local < pad:
+            rows_pad = torch.cat([rows_global,
+                                  torch.full((pad - n_local, m0), EMPTY_SLOT, dtype=torch.int32, device=dev)])
+        g_rows = gather0(rows_pad)
     lv_pad = torch.zeros((pad,), dtype=torch.int16, device=dev)
     lv_pad[:n_local] = torch.from_numpy(lv).to(dev)
     g_levels = gather0(lv_pad)
@@ -445,6 +491,8 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
         timings["stitch_s"] = t_stitch - t_start
         timings["upper_and_gather_s"] = time.perf_counter() - t_stitch
         timings["k_remote"], timings["ef_merge"] = kr, efm
+    if not assemble:
+        result = dict(result or {}, rows=rows_global)
     return result
 
 
@@ -453,7 +501,9 @@ def _assemble_global(shard, world, sizes, bases, n_up, g_slots, g_fp, g_lv, g_ro
     import torch
     n_total = int(bases[-1])
     levels = np.concatenate([g_levels[h][:sizes[h]].cpu().numpy() for h in range(world)]).astype(np.int16)
-    adj0 = np.concatenate([g_rows[h][:sizes[h]].cpu().numpy() for h in range(world)]).view(np.uint32)
+    adj0 = None
+    if g_rows is not None:
+        adj0 = np.concatenate([g_rows[h][:sizes[h]].cpu().numpy() for h in range(world)]).view(np.uint32)
     up_global = np.concatenate([g_slots[h][:n_up[h]].cpu().numpy().astype(np.int64) + bases[h] for h in range(world)])
     up_levels = np.concatenate([g_lv[h][:n_up[h]].cpu().numpy() for h in range(world)]).astype(np.int16)
     upper_off = np.concatenate([[0], np.cumsum(levels.astype(np.int64))])
@@ -476,4 +526,7 @@ def _assemble_global(shard, world, sizes, bases, n_up, g_slots, g_fp, g_lv, g_ro
             adj_upper[first_row[owner] + 1 + rel] = to_global(au)
         entry = int(up_global[sub_entry])
         assert max_level == sub_max + 1
-    return dict(levels=levels, adj0=adj0, adj_upper=adj_upper, entry=entry, max_level=max_level)
+    out = dict(levels=levels, adj_upper=adj_upper, entry=entry, max_level=max_level)
+    if adj0 is not None:
+        out["adj0"] = adj0
+    return out
