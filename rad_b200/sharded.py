@@ -225,8 +225,11 @@ EMPTY_SLOT = -1  # 0xFFFFFFFF in the int32 tensors that carry u32 slots between 
 def stitch_parameters(world: int) -> Tuple[int, int]:
     """(remote candidates per node and shard, ef of the remote searches): with few shards every other shard matters
     (half of a node's true neighbours live there), with many the union of their answers does (measured with
-    scripts/stitch_probe.py: recall of the stitched graph within 0.5 points of the one-piece graph at 2..8 shards)."""
-    return (16, 128) if world <= 3 else (8, 64)
+    scripts/stitch_probe.py: recall of the stitched graph within 0.5 points of the one-piece graph at 2..8 shards;
+    at 8 shards ef 32 gives 0.991 / 0.995 on the routable set where the one-piece graph has 0.979 / 0.996)."""
+    if world <= 3:
+        return 16, 128
+    return (8, 64) if world <= 5 else (8, 32)
 
 
 class DeviceShard:
@@ -316,12 +319,19 @@ class TorchComm:
         self.world = self._dist.get_world_size() if self._dist else 1
         self.rank = self._dist.get_rank() if self._dist else 0
 
+    # every tensor travels as raw bytes: NCCL has no 16-bit integer type, and the payloads are slots, levels and
+    # fingerprints, never numbers to reduce
+    @staticmethod
+    def _bytes(t):
+        import torch
+        return t.contiguous().view(-1).view(torch.uint8)
+
     def all_gather(self, t):
         import torch
         if self.world == 1:
             return t.unsqueeze(0)
         out = torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=t.device)
-        self._dist.all_gather_into_tensor(out.view(-1), t.contiguous().view(-1))
+        self._dist.all_gather_into_tensor(self._bytes(out), self._bytes(t))
         return out
 
     def all_to_all(self, send):
@@ -329,7 +339,7 @@ class TorchComm:
         import torch
         send = send.contiguous()
         recv = torch.empty_like(send)
-        self._dist.all_to_all_single(recv.view(-1), send.view(-1))
+        self._dist.all_to_all_single(self._bytes(recv), self._bytes(send))
         return recv
 
     def gather0(self, t):
@@ -337,7 +347,7 @@ class TorchComm:
         if self.world == 1:
             return [t]
         out = [torch.empty_like(t) for _ in range(self.world)] if self.rank == 0 else None
-        self._dist.gather(t.contiguous(), out, dst=0)
+        self._dist.gather(self._bytes(t), None if out is None else [self._bytes(o) for o in out], dst=0)
         return out
 
     def barrier(self):
@@ -386,46 +396,17 @@ class _LocalRank:
         self._hub._bar.wait()
 
 
-def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 65536,
-                       k_remote: int | None = None, ef_merge: int | None = None, timings: dict | None = None,
-                       comm=None, assemble: bool = True):
-    """ONE HNSW graph with global slots from the sub-graphs every rank built over its own row shard (SURVEY.md §8e
-    row 3).  Collective: every rank calls it with its ``DeviceShard`` and the global slot of its first row; shards
-    are contiguous and ordered by rank.
-
-    1. STITCH, level 0, in rounds of ``batch`` nodes per rank: all-gather of the round's fingerprints (NCCL); every rank
-       answers the other ranks' rows from its own graph (``k_remote`` nearest at ef ``ef_merge``) and sends the answers
-       WITH their fingerprints back (all-to-all); every rank prunes own links + remote candidates with the reference's
-       heuristic into rows of global slots (``rb_stitch_device``).  The sub-graphs themselves stay untouched.
-    2. UPPER LEVELS: the nodes with level >= 1 (1/M of all) are gathered on rank 0 and built there as one graph, one
-       level down; its rows, mapped back to global slots, are levels 1.. of the global graph.
-    Returns on rank 0 ``dict(levels, adj0, adj_upper, entry, max_level)`` (host arrays, global slots) after gathering
-    the stitched rows; ``None`` on the other ranks.  With ``assemble=False`` the stitched level-0 rows STAY on their
-    GPUs: every rank gets ``dict(rows=int32 cuda tensor [n_local, 2M] of global slots)`` and rank 0's dict also holds
-    ``levels, adj_upper, entry, max_level`` -- the device-resident result ``bench.py`` times."""
-    import time
-
+def _stitch_rows(shard, slot_base: int, comm, batch: int, kr: int, efm: int):
+    """The stitch of ONE graph level held as level 0 of ``shard``'s index: every rank's rows after pruning own links +
+    the other shards' answers -> int32 cuda tensor [n_local, row width] of slots in the numbering ``slot_base`` belongs
+    to (EMPTY_SLOT padded).  Collective; the sub-graphs themselves stay untouched."""
     import torch
-    comm = TorchComm() if comm is None else comm
-    world, rank = comm.world, comm.rank
-    all_gather, gather0 = comm.all_gather, comm.gather0
-    dev = shard.device
-    kr, efm = stitch_parameters(world)
-    kr = k_remote or kr
-    efm = ef_merge or efm
-    n_local, m, m0 = len(shard), shard.m, shard.m0
-    t_start = time.perf_counter()
-
-    def sync():
-        if dev.type == "cuda":
-            torch.cuda.synchronize(dev)
-
-    sizes = all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).view(-1).tolist()
-    bases = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
-    assert int(bases[rank]) == int(slot_base), "shards must be contiguous and ordered by rank"
+    world, rank, dev = comm.world, comm.rank, shard.device
+    n_local, m0 = len(shard), shard.m0
+    sizes = comm.all_gather(torch.tensor([n_local], dtype=torch.int64, device=dev)).view(-1).tolist()
     rows_global = torch.full((n_local, m0), EMPTY_SLOT, dtype=torch.int32, device=dev)
     others = [h for h in range(world) if h != rank]
-    # ---- 1. stitch
+    batch = max(1, min(batch, max(sizes)))
     for r0 in range(0, max(sizes), batch):
         cnt = max(0, min(batch, n_local - r0))
         q = torch.zeros((batch, 128), dtype=torch.uint8, device=dev)
@@ -435,98 +416,192 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
             cand_slots = torch.full((cnt, 0), EMPTY_SLOT, dtype=torch.int32, device=dev)
             cand_fp = torch.zeros((cnt, 0, 128), dtype=torch.uint8, device=dev)
         else:
-            allq = all_gather(q)                                            # [world, batch, 128]
+            allq = comm.all_gather(q)                                       # [world, batch, 128]
             counts = [max(0, min(batch, sizes[h] - r0)) for h in range(world)]
             send_slots = torch.full((world, batch, kr), EMPTY_SLOT, dtype=torch.int32, device=dev)
             send_fp = torch.zeros((world, batch, kr, 128), dtype=torch.uint8, device=dev)
             for src in others:
-                if not counts[src]:
+                if not counts[src] or not n_local:
                     continue
                 s, f = shard.remote_candidates(allq[src, :counts[src]].contiguous(), kr, efm)
-                send_slots[src, :counts[src]] = torch.where(s != EMPTY_SLOT, s + int(slot_base), s)  # global slots
+                send_slots[src, :counts[src]] = torch.where(s != EMPTY_SLOT, s + int(slot_base), s)
                 send_fp[src, :counts[src]] = f
-            sync()
+            if dev.type == "cuda":
+                torch.cuda.synchronize(dev)
             recv_slots, recv_fp = comm.all_to_all(send_slots), comm.all_to_all(send_fp)
             # recv[h] = what shard h found for MY rows; own block dropped
             cand_slots = recv_slots[others].permute(1, 0, 2).reshape(batch, len(others) * kr)[:cnt].contiguous()
             cand_fp = recv_fp[others].permute(1, 0, 2, 3).reshape(batch, len(others) * kr, 128)[:cnt].contiguous()
         if cnt:
             shard.stitch(r0, cnt, int(slot_base), cand_slots, cand_fp, rows_global[r0:r0 + cnt])
+    return rows_global, sizes
+
+
+def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 65536,
+                       k_remote: int | None = None, ef_merge: int | None = None, timings: dict | None = None,
+                       comm=None, assemble: bool = True, gather_below: int = 262144):
+    """ONE HNSW graph with global slots from the sub-graphs every rank built over its own row shard (SURVEY.md §8e
+    row 3).  Collective: every rank calls it with its ``DeviceShard`` and the global slot of its first row; shards
+    are contiguous and ordered by rank.
+
+    LEVEL 0 -- the stitch (``_stitch_rows``), in rounds of ``batch`` nodes per rank: all-gather of the round's
+    fingerprints (NCCL); every rank answers the other ranks' rows from its own graph (``k_remote`` nearest at ef
+    ``ef_merge``) and sends the answers WITH their fingerprints back (all-to-all); every rank prunes own links + remote
+    candidates with the reference's heuristic into rows of global slots (``rb_stitch_device``).
+    LEVEL d >= 1 -- the same, recursively: every rank builds a sub-index over ITS nodes with level >= d, one level down
+    (its level 0 = graph level d, rows M wide), and those sub-indexes are stitched like level 0; 1/M of the work of the
+    level below, on all GPUs at once.  Once at most ``gather_below`` nodes remain in total they are gathered on rank 0
+    and all remaining levels are built there as one graph.
+
+    Returns on rank 0 ``dict(levels, adj0, adj_upper, entry, max_level)`` (host arrays, global slots), ``None`` on the
+    other ranks.  With ``assemble=False`` nothing is gathered: every rank gets ``dict(rows=int32 cuda tensor
+    [n_local, 2M], upper=[(graph level, rows int32 [n_d, M], global slots of those nodes int64 [n_d]), ...])`` -- all
+    rows in GLOBAL slots, resident on the GPU that owns the nodes -- and rank 0 also ``top`` (the rank-0 build) --
+    the device-resident result ``bench.py`` times."""
+    import time
+
+    import torch
+    from .index import Index
+    comm = TorchComm() if comm is None else comm
+    world, rank = comm.world, comm.rank
+    dev = shard.device
+    kr, efm = stitch_parameters(world)
+    kr, efm = k_remote or kr, ef_merge or efm
+    n_local, m = len(shard), shard.m
+    t_start = time.perf_counter()
+
+    def sync():
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+
+    def counts_of(n):
+        return comm.all_gather(torch.tensor([n], dtype=torch.int64, device=dev)).view(-1).tolist()
+
+    def padded(t, cap, fill):
+        out = torch.full((cap,) + tuple(t.shape[1:]), fill, dtype=t.dtype, device=dev)
+        out[:len(t)] = t
+        return out
+
+    rows0, sizes = _stitch_rows(shard, int(slot_base), comm, batch, kr, efm)
+    bases = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    assert int(bases[rank]) == int(slot_base), "shards must be contiguous and ordered by rank"
+    assert int(bases[-1]) < (1 << 31), "the stitch addresses at most 2^31 - 1 global slots"
     sync()
     comm.barrier()
     t_stitch = time.perf_counter()
-    # ---- 2. upper levels on rank 0
+    # ---- upper levels
     lv = np.asarray(shard.levels(), dtype=np.int16)
-    up_local = np.flatnonzero(lv >= 1).astype(np.int64)
-    n_up = all_gather(torch.tensor([len(up_local)], dtype=torch.int64, device=dev)).view(-1).tolist()
-    cap = max(max(n_up), 1)
-    up_slots = torch.full((cap,), EMPTY_SLOT, dtype=torch.int32, device=dev)
-    up_fp = torch.zeros((cap, 128), dtype=torch.uint8, device=dev)
-    up_lv = torch.zeros((cap,), dtype=torch.int16, device=dev)
-    if len(up_local):
-        idx = torch.from_numpy(up_local.astype(np.int32)).to(dev)
-        up_slots[:len(up_local)] = idx
-        up_fp[:len(up_local)] = shard.gather_vectors(idx)
-        up_lv[:len(up_local)] = torch.from_numpy(lv[up_local]).to(dev)
-    g_slots, g_fp, g_lv = gather0(up_slots), gather0(up_fp), gather0(up_lv)
-    # the levels and (when assembling) the stitched level-0 rows, padded to the largest shard, to rank 0
-    pad = max(sizes)
-    g_rows = None
-    if assemble:
-        rows_pad = rows_global
-        if n_local < pad:
-            rows_pad = torch.cat([rows_global,
-                                  torch.full((pad - n_local, m0), EMPTY_SLOT, dtype=torch.int32, device=dev)])
-        g_rows = gather0(rows_pad)
-    lv_pad = torch.zeros((pad,), dtype=torch.int16, device=dev)
-    lv_pad[:n_local] = torch.from_numpy(lv).to(dev)
-    g_levels = gather0(lv_pad)
-    result = None
-    if rank == 0:
-        result = _assemble_global(shard, world, sizes, bases, n_up, g_slots, g_fp, g_lv, g_rows, g_levels, m,
-                                  expansion_add)
+    pieces, piece_counts, keep, top, top_built = [], [], [], None, False
+    cur, cur_lv = shard, lv
+    cur_glob = torch.arange(n_local, dtype=torch.int64, device=dev) + int(slot_base)
+    depth = 0
+    while True:
+        up_idx = np.flatnonzero(cur_lv >= 1)
+        n_up = counts_of(len(up_idx))
+        total = int(sum(n_up))
+        if total == 0:
+            break
+        depth += 1
+        idx32 = torch.from_numpy(up_idx.astype(np.int32)).to(dev)
+        up_glob = cur_glob[idx32.long()]
+        sub_lv = (cur_lv[up_idx] - 1).astype(np.int16)
+        fp = cur.gather_vectors(idx32) if len(up_idx) else torch.zeros((0, 128), dtype=torch.uint8, device=dev)
+        cap = max(max(n_up), 1)
+        if world == 1 or total <= gather_below:
+            top_built = True  # (on every rank: the collectives below must stay in step)
+            g_glob = comm.gather0(padded(up_glob, cap, -1))
+            g_fp = comm.gather0(padded(fp, cap, 0))
+            g_lv = comm.gather0(padded(torch.from_numpy(sub_lv).to(dev), cap, 0))
+            if rank == 0:
+                t_glob = torch.cat([g_glob[h][:n_up[h]] for h in range(world)]).cpu().numpy()
+                t_lv = torch.cat([g_lv[h][:n_up[h]] for h in range(world)]).cpu().numpy().astype(np.int16)
+                t_fp = torch.cat([g_fp[h][:n_up[h]].to(dev) for h in range(world)])
+                a0, au, sub_entry, _ = shard.build_upper(t_fp, t_lv, expansion_add)
+                top = dict(level=depth, slots=t_glob, sub_levels=t_lv, a0=a0, au=au, entry=int(t_glob[sub_entry]))
+            break
+        sub = Index(ndim=shard.index.ndim, connectivity=m, expansion_add=expansion_add,
+                    device=dev.index if dev.index is not None else -1, _connectivity_base=m)
+        if len(up_idx):
+            shard._settle()
+            sub.add_device(None, fp.data_ptr(), len(up_idx), levels=sub_lv)
+        ushard = DeviceShard(sub, dev)
+        rows_u, _ = _stitch_rows(ushard, int(sum(n_up[:rank])), comm, batch, kr, efm)
+        # this level's own numbering (rank-major, ascending slot) -> global slots
+        allg = comm.all_gather(padded(up_glob, cap, -1))
+        table = torch.cat([allg[h, :n_up[h]] for h in range(world)] + [torch.tensor([-1], dtype=torch.int64, device=dev)])
+        rows_g = table[torch.where(rows_u < 0, torch.full_like(rows_u, total), rows_u).long()].to(torch.int32)
+        pieces.append((depth, rows_g, up_glob))
+        piece_counts.append(n_up)
+        keep.append(sub)
+        cur, cur_lv, cur_glob = ushard, sub_lv, up_glob
+    entry = None
+    if not top_built and pieces:  # every level was stitched: the entry is the lowest slot of the top level
+        lo = comm.all_gather(torch.tensor([int(pieces[-1][2].min()) if len(pieces[-1][2]) else (1 << 62)],
+                                          dtype=torch.int64, device=dev))
+        entry = int(lo.min())
+    sync()
+    comm.barrier()
+    t_upper = time.perf_counter()
+    if timings is not None:
+        timings["stitch_s"] = t_stitch - t_start
+        timings["upper_levels_s"] = t_upper - t_stitch
+        timings["k_remote"], timings["ef_merge"], timings["stitched_levels"] = kr, efm, 1 + len(pieces)
+    if not assemble:
+        out = dict(rows=rows0, upper=pieces)
+        if rank == 0:
+            out["top"], out["entry"] = top, top["entry"] if top else (entry or 0)
+        return out
+    result = _assemble_global(comm, dev, sizes, bases, lv, rows0, pieces, piece_counts, top, entry, m)
     sync()
     comm.barrier()
     if timings is not None:
-        timings["stitch_s"] = t_stitch - t_start
-        timings["upper_and_gather_s"] = time.perf_counter() - t_stitch
-        timings["k_remote"], timings["ef_merge"] = kr, efm
-    if not assemble:
-        result = dict(result or {}, rows=rows_global)
+        timings["assemble_s"] = time.perf_counter() - t_upper
     return result
 
 
-def _assemble_global(shard, world, sizes, bases, n_up, g_slots, g_fp, g_lv, g_rows, g_levels, m, expansion_add):
-    """Rank 0: the gathered pieces -> host arrays of the global graph; the upper levels are built here."""
+def _assemble_global(comm, dev, sizes, bases, lv, rows0, pieces, piece_counts, top, entry, m):
+    """Gather every rank's rows on rank 0 and lay them out as the host arrays of ONE graph (global slots)."""
     import torch
+    world, rank = comm.world, comm.rank
+    n_local, pad = len(lv), max(max(sizes), 1)
+
+    def padded(t, cap, fill):
+        out = torch.full((cap,) + tuple(t.shape[1:]), fill, dtype=t.dtype, device=dev)
+        out[:len(t)] = t
+        return out
+
+    g_rows = comm.gather0(padded(rows0, pad, EMPTY_SLOT))
+    g_levels = comm.gather0(padded(torch.from_numpy(lv).to(dev), pad, 0))
+    g_pieces = []
+    for (level, rows_g, up_glob), n_up in zip(pieces, piece_counts):
+        cap = max(max(n_up), 1)
+        g_pieces.append((level, n_up, comm.gather0(padded(rows_g, cap, EMPTY_SLOT)),
+                         comm.gather0(padded(up_glob, cap, -1))))
+    if rank != 0:
+        return None
     n_total = int(bases[-1])
     levels = np.concatenate([g_levels[h][:sizes[h]].cpu().numpy() for h in range(world)]).astype(np.int16)
-    adj0 = None
-    if g_rows is not None:
-        adj0 = np.concatenate([g_rows[h][:sizes[h]].cpu().numpy() for h in range(world)]).view(np.uint32)
-    up_global = np.concatenate([g_slots[h][:n_up[h]].cpu().numpy().astype(np.int64) + bases[h] for h in range(world)])
-    up_levels = np.concatenate([g_lv[h][:n_up[h]].cpu().numpy() for h in range(world)]).astype(np.int16)
+    adj0 = np.concatenate([g_rows[h][:sizes[h]].cpu().numpy() for h in range(world)]).view(np.uint32)
     upper_off = np.concatenate([[0], np.cumsum(levels.astype(np.int64))])
     adj_upper = np.full((int(upper_off[-1]), m), 0xFFFFFFFF, dtype=np.uint32)
-    entry, max_level = 0, int(levels.max()) if n_total else 0
-    if len(up_global):
-        fp_all = torch.cat([g_fp[h][:n_up[h]].to(shard.device) for h in range(world)])
-        a0, au, sub_entry, sub_max = shard.build_upper(fp_all, (up_levels - 1).astype(np.int16), expansion_add)
-        table = np.append(up_global, 0xFFFFFFFF).astype(np.uint32)  # sub slot -> global slot, EMPTY -> EMPTY
+    for level, n_up, rows_list, glob_list in g_pieces:
+        rows = np.concatenate([rows_list[h][:n_up[h]].cpu().numpy() for h in range(world)]).view(np.uint32)
+        glob = np.concatenate([glob_list[h][:n_up[h]].cpu().numpy() for h in range(world)])
+        adj_upper[upper_off[glob] + level - 1] = rows
+    if top is not None:
+        t_glob, t_lv, dt = top["slots"], top["sub_levels"].astype(np.int64), top["level"]
+        table = np.append(t_glob, 0xFFFFFFFF).astype(np.uint32)  # sub slot -> global slot, EMPTY -> EMPTY
 
         def to_global(rows):
-            return table[np.where(rows == 0xFFFFFFFF, len(up_global), rows).astype(np.int64)]
+            return table[np.where(rows == 0xFFFFFFFF, len(t_glob), rows).astype(np.int64)]
 
-        first_row = upper_off[up_global]  # the level-1 row of every upper node
-        adj_upper[first_row] = to_global(a0)
-        if len(au):
-            sub_off = np.concatenate([[0], np.cumsum((up_levels - 1).astype(np.int64))])
-            owner = np.repeat(np.arange(len(up_global)), (up_levels - 1).astype(np.int64))
-            rel = np.arange(len(au)) - sub_off[owner]  # 0 = level 2 of the graph
-            adj_upper[first_row[owner] + 1 + rel] = to_global(au)
-        entry = int(up_global[sub_entry])
-        assert max_level == sub_max + 1
-    out = dict(levels=levels, adj_upper=adj_upper, entry=entry, max_level=max_level)
-    if adj0 is not None:
-        out["adj0"] = adj0
-    return out
+        first_row = upper_off[t_glob] + dt - 1  # the node's row on graph level dt = level 0 of the rank-0 build
+        adj_upper[first_row] = to_global(top["a0"])
+        if len(top["au"]):
+            sub_off = np.concatenate([[0], np.cumsum(t_lv)])
+            owner = np.repeat(np.arange(len(t_glob)), t_lv)
+            rel = np.arange(len(top["au"])) - sub_off[owner]  # 0 = graph level dt + 1
+            adj_upper[first_row[owner] + 1 + rel] = to_global(top["au"])
+        entry = top["entry"]
+    max_level = int(levels.max()) if n_total else 0
+    return dict(levels=levels, adj0=adj0, adj_upper=adj_upper, entry=int(entry or 0), max_level=max_level)

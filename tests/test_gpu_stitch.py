@@ -61,7 +61,7 @@ def test_stitch_kernel_is_bit_exact_with_its_cpu_statement():
             assert np.array_equal(f[r, c], db[obase + s[r, c]])
 
 
-def _stitch_on_one_gpu(parts, bounds, ef_add, batch=16384):
+def _stitch_on_one_gpu(parts, bounds, ef_add, batch=16384, gather_below=262144):
     shards = len(parts)
     hub = sharded.LocalComm(shards)
     results, errors = [None] * shards, []
@@ -71,7 +71,7 @@ def _stitch_on_one_gpu(parts, bounds, ef_add, batch=16384):
             import torch
             torch.cuda.set_device(0)
             results[g] = sharded.build_global_graph(sharded.DeviceShard(parts[g]), bounds[g], expansion_add=ef_add,
-                                                    batch=batch, comm=hub.rank_view(g))
+                                                    batch=batch, comm=hub.rank_view(g), gather_below=gather_below)
         except Exception as e:  # noqa: BLE001 -- surface the failure in the main thread
             errors.append(e)
             hub._bar.abort()
@@ -86,13 +86,17 @@ def _stitch_on_one_gpu(parts, bounds, ef_add, batch=16384):
     return results[0]
 
 
-@pytest.mark.parametrize("kind,shards", [("dense", 3), ("analogue", 2)])
-def test_stitched_graph_is_one_valid_graph_with_single_graph_recall(kind, shards, tmp_path):
+@pytest.mark.parametrize("kind,shards,gather_below", [("dense", 3, 262144), ("analogue", 2, 262144),
+                                                      ("dense", 2, 2000), ("dense", 3, 0)])
+def test_stitched_graph_is_one_valid_graph_with_single_graph_recall(kind, shards, gather_below, tmp_path):
+    """gather_below = the number of upper-level nodes from which the remaining levels are built on rank 0: the default
+    (everything above level 0 on rank 0 at this size), 2000 (level 1 stitched across the shards like level 0, levels
+    2.. on rank 0) and 0 (EVERY level stitched)."""
     n, m, ef_add = 90_000, 8, 400
     db = synth.named_set(kind, n, seed=17)
     bounds = [n * g // shards for g in range(shards + 1)]
     parts = _build_shards(db, bounds, m, ef_add)
-    res = _stitch_on_one_gpu(parts, bounds, ef_add)
+    res = _stitch_on_one_gpu(parts, bounds, ef_add, gather_below=gather_below)
     lv, _ = O.levels(n, m)
     assert np.array_equal(res["levels"], lv)  # every shard drew ITS rows of the reference's single level stream
     adj0, adju = res["adj0"], res["adj_upper"]
@@ -129,7 +133,7 @@ def test_stitched_graph_is_one_valid_graph_with_single_graph_recall(kind, shards
         one.expansion_search = ef
         report[ef] = (_recall(whole.search(q, 10).distances, exact.distances),
                       _recall(one.search(q, 10).distances, exact.distances))
-    print(f"\n[stitch] {kind} {n} rows in {shards} shards: " +
+    print(f"\n[stitch] {kind} {n} rows in {shards} shards, gather_below={gather_below}: " +
           ", ".join(f"ef={ef}: stitched {a:.4f} vs one-piece {b:.4f}" for ef, (a, b) in report.items()))
     for ef, (a, b) in report.items():
         assert a >= b - 0.005, (kind, ef, a, b)
