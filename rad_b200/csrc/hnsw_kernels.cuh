@@ -281,34 +281,33 @@ __device__ __forceinline__ uint32_t list_merge(uint64_t* list, uint32_t& len, ui
         pos = 0xFFFFFFFFu;
     }
     const uint32_t pmin = __shfl_sync(RB_FULL_MASK, pos, 0);
-    // entries [pmin, len) move up by the number of candidates in front of them, highest chunk first
-    for (uint32_t hi = len; hi > pmin;) {
-        uint32_t lo = (hi - pmin > 32) ? hi - 32 : pmin;
-        uint32_t idx = lo + lane;
-        bool act = idx < hi;
-        uint64_t v = act ? list[idx] : 0ull;
-        uint32_t c = 0;  // number of candidates with pos <= idx (pos is ascending over lanes)
-#pragma unroll
-        for (uint32_t stp = 16; stp; stp >>= 1) {
-            uint32_t pv = __shfl_sync(RB_FULL_MASK, pos, (int)(c + stp - 1));
-            if (pv <= idx)
-                c += stp;
-        }
-        {
-            uint32_t pv = __shfl_sync(RB_FULL_MASK, pos, 31);
-            if (c == 31 && pv <= idx)
-                c = 32;
-        }
+    // Candidate j lands at fin_j = pos_j + j (strictly ascending over the lanes); every other place o of the merged
+    // list takes list[o - c(o)], c(o) = number of candidates that land below o.  The places [pmin, newlen) are written
+    // 32 at a time from the top down -- a chunk reads at most 32 entries below itself, which the chunks after it have
+    // not written yet -- and per chunk the candidates' places are ONE bit mask (REDUX.OR), so c(o) is two popcounts.
+    const uint32_t newlen = (len + cnt < ef) ? len + cnt : ef;
+    const uint32_t fin = (uint32_t)lane < cnt ? pos + (uint32_t)lane : 0xFFFFFFFFu;
+    const uint32_t below_lane = (1u << lane) - 1u;
+    for (uint32_t hi = newlen; hi > pmin;) {
+        const uint32_t lo = (hi - pmin > 32) ? hi - 32 : pmin;
+        const uint32_t o = lo + lane;
+        const uint32_t cb = __popc(__ballot_sync(RB_FULL_MASK, fin < lo));
+        const uint32_t rel = fin - lo;  // < 32: lands in this chunk
+        const uint32_t cmask = __reduce_or_sync(RB_FULL_MASK, rel < 32u ? 1u << rel : 0u);
+        const uint32_t c = cb + __popc(cmask & below_lane);
+        const bool is_cand = (cmask >> lane) & 1u;
+        const uint64_t ck = __shfl_sync(RB_FULL_MASK, k, (int)(c & 31u));
+        const bool act = o < hi;
+        uint64_t v = ck;
+        if (act && !is_cand)
+            v = list[o - c];
         __syncwarp();
-        if (act && idx + c < ef)
-            list[idx + c] = v;
+        if (act)
+            list[o] = v;
         __syncwarp();
         hi = lo;
     }
-    if ((uint32_t)lane < cnt && pos + lane < ef)
-        list[pos + lane] = k;
-    __syncwarp();
-    len = (len + cnt < ef) ? len + cnt : ef;
+    len = newlen;
     return pmin;
 }
 

@@ -31,9 +31,16 @@ def one(n):
 
 
 if __name__ == "__main__":
-    sizes = [int(a) for a in sys.argv[1:]] or [10000, 30000, 100000, 300000]
+    args = sys.argv[1:]
+    append = "--append" in args  # keep the points already in profiles/ref_counters.json and refit over all of them
+    sizes = [int(a) for a in args if a != "--append"] or [10000, 30000, 100000, 300000]
     with ProcessPoolExecutor(len(sizes)) as ex:
         rows = list(ex.map(one, sizes))
+    path = os.path.join(ROOT, "profiles", "ref_counters.json")
+    if append and os.path.exists(path):
+        with open(path) as fh:
+            old = json.load(fh)["table"]
+        rows = sorted([r for r in old if r["rows"] not in sizes] + rows, key=lambda r: r["rows"])
     x = np.log([r["rows"] for r in rows])
     A = np.stack([np.ones_like(x), x], axis=1)
     d = np.linalg.lstsq(A, np.array([r["distances_per_insert"] for r in rows]), rcond=None)[0]
@@ -42,6 +49,10 @@ if __name__ == "__main__":
            "table": rows, "fit": {"d0": float(d[0]), "d1": float(d[1]), "h0": float(h[0]), "h1": float(h[1])},
            "note": "computed_distances includes the refine and reverse-refine distances (index.hpp:2183-2191)"}
     os.makedirs(os.path.join(ROOT, "profiles"), exist_ok=True)
-    with open(os.path.join(ROOT, "profiles", "ref_counters.json"), "w") as fh:
+    resid = {str(r["rows"]): {"distances": float(r["distances_per_insert"] - (d[0] + d[1] * np.log(r["rows"]))),
+                              "expansions": float(r["expansions_per_insert"] - (h[0] + h[1] * np.log(r["rows"])))}
+             for r in rows}
+    out["fit_residuals"] = resid
+    with open(path, "w") as fh:
         json.dump(out, fh, indent=1)
     print(json.dumps(out, indent=1))
