@@ -950,6 +950,19 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
     RB_CUDA(cudaMemcpy(counters, d.counters, sizeof(counters), cudaMemcpyDeviceToHost));
     ix->last.computed_distances = counters[0];
     ix->last.visited_members = counters[1];
+#ifdef RB_PHASE_TIMING
+    {
+        unsigned long long ph[8], zero[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        RB_CUDA(cudaMemcpyFromSymbol(ph, rb::g_phase, sizeof(ph)));
+        RB_CUDA(cudaMemcpyToSymbol(rb::g_phase, zero, sizeof(zero)));
+        const double s = ph[6] ? (double)ph[6] : 1.0, e = counters[1] ? (double)counters[1] : 1.0;
+        std::fprintf(stderr,
+                     "[rb phase] searches %llu expansions %llu | cycles per search: pick %.0f rows %.0f stage %.0f eval %.0f "
+                     "park %.0f merge %.0f | per expansion: pick %.0f rows %.0f stage %.0f eval %.0f park %.0f merge %.0f\n",
+                     ph[6], counters[1], ph[0] / s, ph[1] / s, ph[2] / s, ph[3] / s, ph[4] / s, ph[5] / s, ph[0] / e,
+                     ph[1] / e, ph[2] / e, ph[3] / e, ph[4] / e, ph[5] / e);
+    }
+#endif
     ix->last.batches = batches.size();
     ix->last.kernel_launches = launches;
     ix->last.device_ms = ms;

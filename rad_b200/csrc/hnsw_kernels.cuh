@@ -316,6 +316,23 @@ struct TraversalCounters {
     uint32_t expansions;
 };
 
+// RB_PHASE_TIMING (development build, scripts/build_variant.sh phase -DRB_PHASE_TIMING): where a warp's cycles go inside
+// warp_beam_search, summed over all warps into g_phase (printed by rb_add when RB_PHASE_PRINT is set).
+#ifdef RB_PHASE_TIMING
+__device__ unsigned long long g_phase[8];
+#define RB_PHASE(k)                                                         \
+    do {                                                                    \
+        const long long now_ = clock64();                                   \
+        if (lane == 0)                                                      \
+            phase_smem[(threadIdx.x >> 5) * 8 + (k)] += (uint32_t)(now_ - phase_t); \
+        phase_t = now_;                                                     \
+    } while (0)
+#else
+#define RB_PHASE(k) \
+    do {            \
+    } while (0)
+#endif
+
 // ------------------------------------------------------------------------------------------------ greedy descent
 // index.hpp:3935-3975: move to the best neighbour until no neighbour improves, on levels (from, to].
 __device__ __forceinline__ void warp_greedy_descent(const GraphView& g, uint4 q4, uint32_t& cur, uint32_t& cur_bits,
@@ -355,6 +372,13 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
                                                      uint32_t start_bits, int level, uint32_t ef,
                                                      TraversalCounters& tc) {
     const int lane = threadIdx.x & 31;
+#ifdef RB_PHASE_TIMING
+    __shared__ uint32_t phase_smem[kWarpsPerBlock * 8];
+    if (lane < 8)
+        phase_smem[(threadIdx.x >> 5) * 8 + lane] = 0;
+    __syncwarp();
+    long long phase_t = clock64();
+#endif
     // clear the filter
     {
         uint4* b4 = reinterpret_cast<uint4*>(w.bloom);
@@ -390,6 +414,7 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
     const uint32_t row_width = level == 0 ? g.m0 : g.m;
     const bool two = row_width <= 16;
     for (;;) {
+        RB_PHASE(4);  // keep + park (and the set-up before the first iteration)
         // first (two) unexpanded entries of the list
         uint32_t pos1 = 0xFFFFFFFFu, pos2 = 0xFFFFFFFFu;
         for (uint32_t base = hint; base < len; base += 32) {
@@ -413,11 +438,13 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
             // (or when the list ran out of open entries) merge now and look again.
             const uint32_t last = two ? pos2 : pos1;
             if (last == 0xFFFFFFFFu || last + pn >= ef) {
+                RB_PHASE(0);
                 uint32_t at = list_merge(w.list, len, ef, pk, (uint32_t)lane < pn);
                 if (at < hint)
                     hint = at;
                 pn = 0;
                 pk = ~0ull;
+                RB_PHASE(5);  // merges
                 continue;
             }
         }
@@ -482,6 +509,7 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
             hint = took2 ? pos2 + 1 : took1 ? pos1 + 1 : pos1;
         }
         tc.expansions += both ? 2 : 1;
+        RB_PHASE(0);  // scan + flush check + pick + mark
         uint32_t nid = RB_EMPTY, npc = 0;
         {
             const bool upper_half = two && lane >= 16;
@@ -500,6 +528,7 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
             fresh = fresh && (uint32_t)(__ffs((int)same) - 1) == (uint32_t)lane;
         }
         __syncwarp();  // every lane has tested against the state before this iteration
+        RB_PHASE(1);  // link-row loads until the filter has been consulted
         if (fresh)
             bloom_set(w.bloom, nid, w.bloom_log2);
         uint32_t mask = __ballot_sync(RB_FULL_MASK, fresh);
@@ -512,9 +541,11 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         const uint2 staged = (uint32_t)lane < cnt ? w.ids[lane] : make_uint2(0u, 0u);
         const uint32_t id = staged.x;
         __syncwarp();
+        RB_PHASE(2);  // filter update + staging
         uint32_t cand;  // the candidate whose distance this lane received
         uint32_t bits = warp_eval4(g.fp, qa, qb, id, staged.y, pq, cnt, cand);
         tc.distances += cnt;
+        RB_PHASE(3);  // evaluation (fingerprint loads + counts + divide)
         // qualify against the (possibly stale, hence only looser) worst list entry and park in pending
         const uint64_t key = make_key(bits, __shfl_sync(RB_FULL_MASK, id, cand & 31));
         bool keep = cand != 0xFFFFFFFFu && (len < ef || key < (w.list[ef - 1] & ~1ull));
@@ -523,10 +554,12 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         if (!kc)
             continue;
         if (pn + kc > 32) {
+            RB_PHASE(4);
             uint32_t at = list_merge(w.list, len, ef, pk, (uint32_t)lane < pn);
             if (at < hint)
                 hint = at;
             pn = 0;
+            RB_PHASE(5);
         }
         if (keep)
             w.pend[pn + __popc(kmask & ((1u << lane) - 1u))] = key;
@@ -534,6 +567,14 @@ __device__ __forceinline__ uint32_t warp_beam_search(const GraphView& g, const W
         __syncwarp();
         pk = (uint32_t)lane < pn ? w.pend[lane] : ~0ull;
     }
+#ifdef RB_PHASE_TIMING
+    RB_PHASE(0);
+    __syncwarp();
+    if (lane < 8)
+        atomicAdd(&g_phase[lane], (unsigned long long)phase_smem[(threadIdx.x >> 5) * 8 + lane]);
+    if (lane == 0)
+        atomicAdd(&g_phase[6], 1ull);  // searches (index 6 also took the unused slot's zero above)
+#endif
     return len;
 }
 
