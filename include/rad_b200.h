@@ -171,6 +171,20 @@ RB_EXPORT void rb_synth_fingerprints_device_ex(void* d_out, uint64_t first_row, 
                                                uint64_t rows_per_centre, uint64_t dup_fold, uint64_t dup_start,
                                                uint64_t dup_rows, uintptr_t stream, rb_error_t* error);
 
+/* ---------------------------------------------------------------- fingerprint ingest.
+ * The reference has no pre-pass: identical fingerprints are inserted like any other row (index.hpp:2734-2834) and form
+ * d = 0 cliques that fill their members' M links and inflate every ef-bounded search that meets them; its clustering /
+ * join helpers (python/usearch/index.py:1182-1273) start from the same rows.
+ * rb_dedup_device: d_representative[i] (u32) = the LOWEST row whose 128 bytes equal row i's (== i for a fingerprint seen
+ * for the first time).  d_vectors: rows x 128 bytes on the device; the workspace is rb_dedup_workspace_bytes(rows)
+ * (about 28 bytes per row).  Runs on `stream`, no synchronisation; the answer never depends on the internal hash.
+ * rb_popcounts_device: d_popcounts[i] (u16) = number of set bits of row i (the |a| of union = |a| + |q| - intersection). */
+RB_EXPORT size_t rb_dedup_workspace_bytes(uint64_t rows);
+RB_EXPORT void rb_dedup_device(void const* d_vectors, uint64_t rows, void* d_representative, void* d_workspace,
+                               size_t workspace_bytes, uintptr_t stream, rb_error_t* error);
+RB_EXPORT void rb_popcounts_device(void const* d_vectors, uint64_t rows, void* d_popcounts, uintptr_t stream,
+                                   rb_error_t* error);
+
 /* ---------------------------------------------------------------- one graph from G row shards (SURVEY.md section 8e row 3;
  * usearch has no counterpart: its multi-index `Indexes`, python/lib.cpp:417-498, only searches shards side by side).
  * Every shard is built on its own GPU; then every node searches the OTHER shards (rb_search_device on their handles),

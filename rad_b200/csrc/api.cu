@@ -18,6 +18,7 @@
 #include <vector>
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <cuda_runtime.h>
 
 #include "../../include/rad_b200.h"
@@ -25,6 +26,7 @@
 #include "exact_i8_kernels.cuh"
 #include "hnsw_kernels.cuh"
 #include "host_index.hpp"
+#include "ingest_kernels.cuh"
 #include "synth_kernels.cuh"
 
 namespace {
@@ -1820,6 +1822,91 @@ void rb_merge_topk_device(void const* d_partial_keys, uint32_t parts, uint64_t q
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
         RB_FAIL(std::string("CUDA error in merge: ") + cudaGetErrorString(e));
+}
+
+// ---------------------------------------------------------------------------------------------- ingest: duplicates
+namespace {
+struct DedupLayout {
+    size_t hashes[2], ids[2], start, tmp, tmp_bytes, total;
+};
+DedupLayout dedup_layout(uint64_t rows) {
+    DedupLayout L{};
+    auto take = [&](size_t bytes) {
+        size_t at = L.total;
+        L.total += (bytes + 255) & ~(size_t)255;
+        return at;
+    };
+    L.hashes[0] = take(rows * 8), L.hashes[1] = take(rows * 8);
+    L.ids[0] = take(rows * 4), L.ids[1] = take(rows * 4);
+    L.start = take(rows * 4);
+    size_t sort_tmp = 0, scan_tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, (uint64_t*)nullptr, (uint64_t*)nullptr, (uint32_t*)nullptr,
+                                    (uint32_t*)nullptr, (int64_t)rows);
+    cub::DeviceScan::InclusiveScan(nullptr, scan_tmp, (uint32_t*)nullptr, (uint32_t*)nullptr, cub::Max(), (int64_t)rows);
+    L.tmp_bytes = std::max(sort_tmp, scan_tmp);
+    L.tmp = take(L.tmp_bytes);
+    return L;
+}
+}  // namespace
+
+size_t rb_dedup_workspace_bytes(uint64_t rows) { return rows ? dedup_layout(rows).total : 0; }
+
+void rb_dedup_device(void const* d_vectors, uint64_t rows, void* d_representative, void* d_workspace,
+                     size_t workspace_bytes, uintptr_t stream_, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!rows)
+        return;
+    if (rows >= (1ull << 32))
+        RB_FAIL("rb_dedup_device addresses at most 2^32 - 1 rows");
+    const DedupLayout L = dedup_layout(rows);
+    if (workspace_bytes < L.total)
+        RB_FAIL("workspace smaller than rb_dedup_workspace_bytes(rows)");
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    uint8_t* ws = static_cast<uint8_t*>(d_workspace);
+    uint64_t* h0 = reinterpret_cast<uint64_t*>(ws + L.hashes[0]);
+    uint64_t* h1 = reinterpret_cast<uint64_t*>(ws + L.hashes[1]);
+    uint32_t* i0 = reinterpret_cast<uint32_t*>(ws + L.ids[0]);
+    uint32_t* i1 = reinterpret_cast<uint32_t*>(ws + L.ids[1]);
+    uint32_t* start = reinterpret_cast<uint32_t*>(ws + L.start);
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned grid8 = (unsigned)std::min<uint64_t>((rows * 8 + 255) / 256, (uint64_t)sms * 16);
+    const unsigned grid1 = (unsigned)std::min<uint64_t>((rows + 255) / 256, (uint64_t)sms * 16);
+    const uint4* fp = static_cast<const uint4*>(d_vectors);
+    rb::row_hash_kernel<<<grid8, 256, 0, stream>>>(fp, rows, h0, i0);
+    size_t tmp = L.tmp_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(ws + L.tmp, tmp, h0, h1, i0, i1, (int64_t)rows, 0, 64, stream);
+    if (e == cudaSuccess) {
+        rb::run_start_kernel<<<grid1, 256, 0, stream>>>(h1, rows, start);
+        tmp = L.tmp_bytes;
+        e = cub::DeviceScan::InclusiveScan(ws + L.tmp, tmp, start, start, cub::Max(), (int64_t)rows, stream);
+    }
+    if (e == cudaSuccess) {
+        rb::representative_kernel<<<grid8, 256, 0, stream>>>(fp, rows, i1, start, static_cast<uint32_t*>(d_representative));
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in dedup: ") + cudaGetErrorString(e));
+}
+
+void rb_popcounts_device(void const* d_vectors, uint64_t rows, void* d_popcounts, uintptr_t stream_, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!rows)
+        return;
+    if (rows >= (1ull << 32))
+        RB_FAIL("rb_popcounts_device addresses at most 2^32 - 1 rows");
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const unsigned grid = (unsigned)std::min<uint64_t>((rows * 8 + 255) / 256, (uint64_t)sms * 16);
+    rb::node_popcount_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream_)>>>(
+        static_cast<const uint4*>(d_vectors), (uint32_t)rows, static_cast<uint16_t*>(d_popcounts));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in popcounts: ") + cudaGetErrorString(e));
 }
 
 void rb_unpack_topk_device(void const* d_keys, uint64_t query_count, uint32_t k, void* d_slots_out,

@@ -265,10 +265,16 @@ class Index:
         return int(self._lib.rb_size(self._handle()))
 
     def add(self, keys, vectors, *, copy: bool = True, threads: int = 0, log: Union[str, bool] = False,
-            progress: Optional[ProgressCallback] = None):
+            progress: Optional[ProgressCallback] = None, dedup: bool = False):
         """Insert one or many fingerprints (reference: index.py:631-678, :224-279, lib.cpp:223-268).
-        ``threads`` is accepted and ignored: the build runs as batched CUDA kernels."""
+        ``threads`` is accepted and ignored: the build runs as batched CUDA kernels.  ``dedup=True`` (additive, empty
+        index only) keeps exact duplicates out of the graph search and chains them behind their first occurrence
+        (``rad_b200.ingest.add_deduplicated``)."""
         assert isinstance(vectors, np.ndarray), "Expects a NumPy array"
+        if dedup:
+            from . import ingest
+            ingest.add_deduplicated(self, keys, vectors.reshape(1, -1) if vectors.ndim == 1 else vectors)
+            return self.keys
         assert not progress or _match_signature(progress, [int, int], bool), "Invalid callback"
         assert vectors.ndim == 1 or vectors.ndim == 2, "Expects a matrix or vector"
         if vectors.ndim == 1:
