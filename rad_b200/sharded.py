@@ -189,8 +189,96 @@ class ShardedIndex:
         return t
 
     def search(self, vectors, count: int = 10, *, exact: bool = False):
-        from .index import BatchMatches
+        """Merged k-NN over all shards, the same ``BatchMatches`` on every rank.  Under NCCL the answers never leave
+        the GPUs until they are merged (``search_device``); under gloo (CPU tests) the merge is the numpy statement."""
         vectors = np.atleast_2d(vectors)
+        if self._dist is not None and self._dist.get_backend() == "nccl" and hasattr(self.local, "_handle"):
+            return self._search_on_device(vectors, count, exact)
+        return self._search_on_host(vectors, count, exact)
+
+    # ---- device-resident path: rb_search_device -> keys on the GPU -> all-gather -> rb_merge_topk_device -> user keys
+    def _device_keys(self, device):
+        """this shard's user keys as an int64 CUDA tensor (uploaded once per index size)"""
+        n = len(self.local)
+        cached = getattr(self, "_d_user_keys", None)
+        if cached is None or cached.numel() != n or cached.device != device:
+            keys = np.ascontiguousarray(np.asarray(self.local.keys, dtype=np.uint64)).view(np.int64)
+            cached = self._torch.from_numpy(keys).to(device)
+            self._d_user_keys = cached
+        return cached
+
+    def local_answers_device(self, d_queries, count: int, exact: bool):
+        """This shard's answers for CUDA queries ``uint8 [Q, 128]`` -> (merge keys int64 [Q, k] = distance bits << 32 |
+        ~GLOBAL slot, -1 padded; the users' keys of those answers int64 [Q, k])."""
+        torch = self._torch
+        from . import _native
+        dev = d_queries.device
+        nq = int(d_queries.shape[0])
+        slots = torch.zeros((nq, count), dtype=torch.int32, device=dev)
+        dists = torch.zeros((nq, count), dtype=torch.float32, device=dev)
+        counts = torch.zeros((nq,), dtype=torch.int32, device=dev)
+        if nq and len(self.local):
+            torch.cuda.current_stream(dev).synchronize()  # the library works on the handle's own stream
+            err = C.c_char_p()
+            _native.lib().rb_search_device(self.local._handle(), d_queries.data_ptr(), nq, count, 1 if exact else 0,
+                                           slots.data_ptr(), dists.data_ptr(), counts.data_ptr(), C.byref(err))
+            _native.check(err)
+        valid = torch.arange(count, device=dev)[None, :] < counts[:, None]
+        local = torch.where(valid, slots, torch.zeros_like(slots)).long()
+        inv_global = (~(local + self.slot_base)) & 0xFFFFFFFF
+        mkeys = (dists.view(torch.int32).long() << 32) | inv_global
+        mkeys = torch.where(valid, mkeys, torch.full_like(mkeys, -1))
+        ukeys = self._device_keys(dev)[local] if len(self.local) else torch.zeros_like(mkeys)
+        return mkeys, torch.where(valid, ukeys, torch.zeros_like(ukeys))
+
+    @staticmethod
+    def merge_answers_device(all_mkeys, all_ukeys, count: int):
+        """``[W, Q, k]`` merge keys and user keys of all shards -> (user keys [Q, k], distances f32 [Q, k], counts
+        int64 [Q]) after ``rb_merge_topk_device`` (the merge rule of index.hpp:2625-2645), all on the device."""
+        import torch
+        from . import _native
+        world, nq, k = all_mkeys.shape
+        merged = torch.empty((nq, count), dtype=torch.int64, device=all_mkeys.device)
+        err = C.c_char_p()
+        _native.lib().rb_merge_topk_device(all_mkeys.contiguous().data_ptr(), world, nq, k, merged.data_ptr(),
+                                           torch.cuda.current_stream(all_mkeys.device).cuda_stream, C.byref(err))
+        _native.check(err)
+        # where each merged key came from among the world * k gathered ones (global slots are unique)
+        flat_m = all_mkeys.permute(1, 0, 2).reshape(nq, world * k)
+        flat_u = all_ukeys.permute(1, 0, 2).reshape(nq, world * k)
+        src = (flat_m[:, None, :] == merged[:, :, None]).int().argmax(dim=2)
+        valid = merged != -1
+        out_keys = torch.where(valid, torch.gather(flat_u, 1, src), torch.zeros_like(merged))
+        out_d = torch.where(valid, (merged >> 32).int().view(torch.float32), torch.zeros((), device=merged.device))
+        return out_keys, out_d, valid.sum(dim=1)
+
+    def search_device(self, d_queries, count: int = 10, *, exact: bool = False):
+        """CUDA queries in, CUDA answers out: (user keys int64 [Q, k], distances f32 [Q, k], counts int64 [Q])."""
+        torch = self._torch
+        mkeys, ukeys = self.local_answers_device(d_queries, count, exact)
+        both = torch.stack([mkeys, ukeys])                                      # [2, Q, k]
+        gathered = torch.empty((self.world,) + tuple(both.shape), dtype=both.dtype, device=both.device)
+        if self.world > 1:
+            self._dist.all_gather_into_tensor(gathered.view(-1), both.view(-1))
+        else:
+            gathered[0] = both
+        return self.merge_answers_device(gathered[:, 0].contiguous(), gathered[:, 1].contiguous(), count)
+
+    def _search_on_device(self, vectors, count, exact):
+        from .index import BatchMatches
+        torch = self._torch
+        dev = torch.device("cuda", torch.cuda.current_device())
+        q = np.ascontiguousarray(vectors, dtype=np.uint8)
+        d_q = torch.zeros((len(q), 128), dtype=torch.uint8, device=dev)
+        d_q[:, :q.shape[1]] = torch.from_numpy(q).to(dev)
+        keys, dists, counts = self.search_device(d_q, count, exact=exact)
+        c = self.local.last_counters if hasattr(self.local, "last_counters") else {}
+        return BatchMatches(keys=keys.cpu().numpy().view(np.uint64), distances=dists.cpu().numpy(),
+                            counts=counts.cpu().numpy(), visited_members=int(c.get("visited_members", 0)),
+                            computed_distances=int(c.get("computed_distances", 0)))
+
+    def _search_on_host(self, vectors, count, exact):
+        from .index import BatchMatches
         got = self.local.search(vectors, count, exact=exact)
         nq = len(vectors)
         keys = np.asarray(got.keys, dtype=np.uint64).reshape(nq, count)
