@@ -62,25 +62,7 @@ static_assert(kTStages <= 8, "barrier arrays");
 static_assert(kTensorSmemBytes <= 232448, "227 KB of shared memory per CTA");
 
 // ---------------------------------------------------------------------------------------------- PTX helpers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(void* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(void* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(void* bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"  // %3: suspend-time hint, the thread
-            "selp.b32 %0, 1, 0, p;\n\t}"                                        // sleeps instead of re-polling
-            : "=r"(done)
-            : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)
-            : "memory");
-    } while (!done);
-}
+// (smem_u32, mbar_init, mbar_arrive, mbar_wait: device_common.cuh)
 // ---- cluster (CTA pair) variants: barriers and popcounts of the peer CTA are reached through shared::cluster addresses
 __device__ __forceinline__ uint32_t cluster_rank() {
     uint32_t r;

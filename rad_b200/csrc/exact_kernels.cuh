@@ -56,6 +56,7 @@ struct ExactSmem {
     uint4 thr[kXQ];  // x = A = u_t + i_t, y = i_t, z = B = i_t * |q|, w = slack (1 while the list is not full)
     uint32_t queue[kXQ * kXD];
     uint32_t queue_count;
+    unsigned long long full[2];  // mbarriers: the bulk copies of database stage 0 / 1 have landed
 };
 
 // insert (key, iu) into an ascending list of exactly k entries (~0 = empty tail) in GLOBAL memory; warp-uniform args
@@ -132,35 +133,56 @@ __global__ void __launch_bounds__(kXThreads, 2) exact_topk_kernel(ExactParams p)
     if (row_begin >= row_end)
         return;  // (uniform) an empty chunk still publishes empty partial lists
     const uint64_t n_tiles = (row_end - row_begin + kXD - 1) / kXD;
-    uint4 stage[2];
-    auto fetch = [&](uint64_t tile) {
+    // The database stage is brought in by the bulk-asynchronous copy engine (cp.async.bulk, the linear form of TMA):
+    // one 128-byte copy per row straight into its padded shared-memory row, completion counted in bytes on the
+    // stage's mbarrier -- no registers and no LDG/STS issue slots on the POPC-bound threads.  Rows past the end of the
+    // chunk are zero-filled by the threads themselves.
+    if (tid == 0) {
+        mbar_init(&s.full[0], 1);
+        mbar_init(&s.full[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto fetch = [&](int buf, uint64_t tile) {  // (the stage was last read before the preceding __syncthreads)
+        if (tid < kXD) {
+            const uint64_t first = row_begin + tile * kXD, row = first + tid;
+            if (tid == 0) {
+                const uint64_t valid = row_end - first < (uint64_t)kXD ? row_end - first : (uint64_t)kXD;
+                mbar_arrive_expect_tx(&s.full[buf], (uint32_t)valid * 128u);
+            }
+            uint32_t* dst = &s.d[buf][tid * kXStride];
+            if (row < row_end) {
+                bulk_load(dst, p.db + row * 8, 128u, &s.full[buf]);
+            } else {
 #pragma unroll
-        for (int pass = 0; pass < 2; ++pass) {
-            uint64_t row = row_begin + tile * kXD + lrow + 32 * pass;
-            stage[pass] = row < row_end ? __ldg(p.db + row * 8 + lsub) : make_uint4(0, 0, 0, 0);
+                for (int w = 0; w < 8; ++w)
+                    reinterpret_cast<uint4*>(dst)[w] = make_uint4(0, 0, 0, 0);
+            }
         }
     };
-    auto commit = [&](int buf, uint64_t tile) {
+    // row popcounts of a landed stage (8 threads per row)
+    auto commit = [&](int buf, uint64_t tile, uint32_t parity) {
+        mbar_wait(&s.full[buf], parity);
 #pragma unroll
         for (int pass = 0; pass < 2; ++pass) {
             int r = lrow + 32 * pass;
             uint64_t row = row_begin + tile * kXD + r;
-            *reinterpret_cast<uint4*>(&s.d[buf][r * kXStride + 4 * lsub]) = stage[pass];
-            uint32_t pc = group8_sum(popc4(stage[pass]));
+            const uint4 v = *reinterpret_cast<const uint4*>(&s.d[buf][r * kXStride + 4 * lsub]);
+            uint32_t pc = group8_sum(popc4(v));
             if (lsub == 0)
                 s.pd[buf][r] = row < row_end ? pc : kXInvalid;
         }
     };
 
-    fetch(n_tiles - 1);
-    commit(0, n_tiles - 1);
+    fetch(0, n_tiles - 1);
+    commit(0, n_tiles - 1, 0);
     __syncthreads();
 
     int buf = 0;
     for (uint64_t it = 0; it < n_tiles; ++it) {
         const uint64_t tile = n_tiles - 1 - it;  // highest rows first
         if (it + 1 < n_tiles)
-            fetch(tile - 1);
+            fetch(buf ^ 1, tile - 1);
 
         // ---- 4 x 4 intersections over 32 words
         uint32_t acc[4][4];
@@ -234,7 +256,7 @@ __global__ void __launch_bounds__(kXThreads, 2) exact_topk_kernel(ExactParams p)
         if (tid == 0)
             s.queue_count = 0;
         if (it + 1 < n_tiles)
-            commit(buf ^ 1, tile - 1);
+            commit(buf ^ 1, tile - 1, (uint32_t)(((it + 1) >> 1) & 1));  // the (it + 1) / 2-th use of that stage
         __syncthreads();
         buf ^= 1;
     }

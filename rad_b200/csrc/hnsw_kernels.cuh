@@ -733,8 +733,20 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_search_kerne
             const uint32_t len = warp_beam_search(p.g, w, q4, cur, cur_bits, level, p.ef, tc);
             const size_t idx = (size_t)p.level_off[level] + t;
             uint64_t* out = p.lists + idx * p.ef;
-            for (uint32_t i = lane; i < len; i += 32)
-                out[i] = w.list[i];
+            // the sorted list leaves shared memory as ONE bulk-asynchronous store (cp.async.bulk, 16-byte granules: an
+            // even number of entries, which an even ef always leaves room for) instead of a copy loop of the warp
+            const bool bulk_out = (p.ef & 1u) == 0;
+            if (bulk_out) {
+                fence_async_proxy();  // every lane's list writes -> visible to the copy engine
+                __syncwarp();
+                if (lane == 0) {
+                    bulk_store(out, w.list, ((len + 1u) & ~1u) * 8u);
+                    bulk_store_commit();
+                }
+            } else {
+                for (uint32_t i = lane; i < len; i += 32)
+                    out[i] = w.list[i];
+            }
             // seed of the batch tile: the exact counts of the list entry at rank min(ef, kSeedRank)
             unsigned long long seed = ~0ull;
             const uint32_t seed_rank = p.ef < (uint32_t)kSeedRank ? p.ef : (uint32_t)kSeedRank;
@@ -751,6 +763,8 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) insert_search_kerne
             const uint64_t k0 = w.list[0];
             cur = key_slot(k0);
             cur_bits = key_bits(k0);
+            if (bulk_out && lane == 0)
+                bulk_store_wait_read();  // the list may be overwritten by the next search
             __syncwarp();
         }
     }
@@ -780,6 +794,13 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) insert_select_kernel(Inse
         w.ids = nullptr;
         w.bloom_log2 = 0;
     }
+    __shared__ unsigned long long list_bar[kWarpsPerBlock];  // one mbarrier per warp for its bulk list loads
+    uint32_t bar_parity = 0;
+    if (lane == 0) {
+        mbar_init(&list_bar[warp], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
     TraversalCounters tc{0, 0};
     for (;;) {
         uint32_t t = 0;
@@ -797,8 +818,20 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) insert_select_kernel(Inse
             uint32_t len = p.lens[idx];
             {
                 const uint64_t* in = p.lists + idx * p.ef;
-                for (uint32_t i = lane; i < len; i += 32)
-                    w.list[i] = in[i];
+                if ((p.ef & 1u) == 0 && len) {  // one bulk-asynchronous copy, completion counted on the warp's mbarrier
+                    const uint32_t bytes = ((len + 1u) & ~1u) * 8u;
+                    fence_async_proxy();
+                    __syncwarp();  // the previous task's reads and writes of the list are done
+                    if (lane == 0) {
+                        mbar_arrive_expect_tx(&list_bar[warp], bytes);
+                        bulk_load(w.list, in, bytes, &list_bar[warp]);
+                    }
+                    mbar_wait(&list_bar[warp], bar_parity);
+                    bar_parity ^= 1u;
+                } else {
+                    for (uint32_t i = lane; i < len; i += 32)
+                        w.list[i] = in[i];
+                }
             }
             __syncwarp();
             if (p.use_mates) {
