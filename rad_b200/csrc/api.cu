@@ -263,28 +263,25 @@ std::string upload_rows(rb_index* ix, uint8_t const* src, size_t count, size_t s
 }
 
 // after rb_load: push the host graph and fingerprints to the device
-std::string upload_graph(rb_index* ix) {
+// the graph of `n` nodes given as host arrays -> device (fingerprints, link rows, offsets, levels, link popcounts)
+std::string upload_arrays(rb_index* ix, size_t n, uint8_t const* vectors, uint32_t const* adj0, uint32_t const* adju,
+                          uint64_t const* upper_off, int16_t const* levels) {
     rbh::HostIndex& h = ix->host;
     DeviceState& d = ix->dev;
-    const size_t n = h.keys.size();
-    if (ix->device_graph_valid)
-        return {};
-    if (n && h.host_vectors.empty())
-        return "The fingerprints of this index are not available (loaded with exclude_vectors)";
-    std::string err = ensure_capacity(ix, n, h.upper_off[n]);
+    std::string err = ensure_capacity(ix, n, upper_off[n]);
     if (!err.empty())
         return err;
     if (n) {
-        if (!(err = upload_rows(ix, h.host_vectors.data(), n, h.vec_bytes, 0)).empty())
+        if (!(err = upload_rows(ix, vectors, n, h.vec_bytes, 0)).empty())
             return err;
-        RB_CUDA(cudaMemcpyAsync(d.adj0, h.adj0.data(), n * h.m0 * 4, cudaMemcpyHostToDevice, d.stream));
-        if (h.upper_off[n])
-            RB_CUDA(cudaMemcpyAsync(d.adju, h.adju.data(), h.upper_off[n] * h.m * 4, cudaMemcpyHostToDevice, d.stream));
+        RB_CUDA(cudaMemcpyAsync(d.adj0, adj0, n * h.m0 * 4, cudaMemcpyHostToDevice, d.stream));
+        if (upper_off[n])
+            RB_CUDA(cudaMemcpyAsync(d.adju, adju, upper_off[n] * h.m * 4, cudaMemcpyHostToDevice, d.stream));
         std::vector<uint32_t> off32(n);
         std::vector<int8_t> lv8(n);
         for (size_t i = 0; i < n; ++i) {
-            off32[i] = (uint32_t)h.upper_off[i];
-            lv8[i] = (int8_t)h.levels[i];
+            off32[i] = (uint32_t)upper_off[i];
+            lv8[i] = (int8_t)levels[i];
         }
         RB_CUDA(cudaMemcpyAsync(d.upper_off, off32.data(), n * 4, cudaMemcpyHostToDevice, d.stream));
         RB_CUDA(cudaMemcpyAsync(d.levels, lv8.data(), n, cudaMemcpyHostToDevice, d.stream));
@@ -294,9 +291,9 @@ std::string upload_graph(rb_index* ix) {
         const unsigned grid = (unsigned)std::min<size_t>((n * 8 + 255) / 256, (size_t)d.sm_count * 16);
         rb::node_popcount_kernel<<<grid, 256, 0, d.stream>>>(d.fp, (uint32_t)n, node_pc);
         rb::link_popcount_kernel<<<(unsigned)d.sm_count * 8, 256, 0, d.stream>>>(d.adj0, n * (size_t)h.m0, node_pc, d.pc0);
-        if (h.upper_off[n])
+        if (upper_off[n])
             rb::link_popcount_kernel<<<(unsigned)d.sm_count * 8, 256, 0, d.stream>>>(
-                d.adju, h.upper_off[n] * (size_t)h.m, node_pc, d.pcu);
+                d.adju, upper_off[n] * (size_t)h.m, node_pc, d.pcu);
         cudaError_t le = cudaGetLastError();
         cudaError_t se = cudaStreamSynchronize(d.stream);
         cudaFree(node_pc);
@@ -304,11 +301,56 @@ std::string upload_graph(rb_index* ix) {
         RB_CUDA(se);
     }
     d.rows = n;
-    d.upper_rows = h.upper_off[n];
+    d.upper_rows = upper_off[n];
     ix->device_graph_valid = true;
+    return {};
+}
+
+std::string upload_graph(rb_index* ix) {
+    rbh::HostIndex& h = ix->host;
+    const size_t n = h.keys.size();
+    if (ix->device_graph_valid)
+        return {};
+    if (n && h.host_vectors.empty())
+        return "The fingerprints of this index are not available (loaded with exclude_vectors)";
+    std::string err = upload_arrays(ix, n, h.host_vectors.data(), h.adj0.data(), h.adju.data(), h.upper_off.data(),
+                                    h.levels.data());
+    if (!err.empty())
+        return err;
     h.host_vectors.clear();
     h.host_vectors.shrink_to_fit();
     return {};
+}
+
+// A VIEWED index (mmap of a .usearch file, index_dense.hpp:1267-1415) is searched like the reference searches it: the
+// graph and the fingerprints are read from the mapping -- here once, into HBM; the host side keeps serving from the file.
+std::string upload_view(rb_index* ix) {
+    rbh::HostIndex& h = ix->host;
+    if (ix->device_graph_valid)
+        return {};
+    const size_t n = h.size();
+    if (n && !h.viewed_vectors())
+        return "The fingerprints of this index are not available (viewed with exclude_vectors)";
+    std::vector<uint64_t> upper_off(n + 1, 0);
+    std::vector<int16_t> levels(n);
+    for (size_t i = 0; i < n; ++i) {
+        levels[i] = (int16_t)h.level_of(i);
+        upper_off[i + 1] = upper_off[i] + (uint64_t)levels[i];
+    }
+    std::vector<uint32_t> adj0(n * (size_t)h.m0, RB_EMPTY), adju(upper_off[n] * (size_t)h.m, RB_EMPTY);
+    const unsigned nt = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < nt; ++t)
+        pool.emplace_back([&, t] {
+            for (size_t i = n * t / nt; i < n * (t + 1) / nt; ++i) {
+                h.neighbors(i, 0, adj0.data() + i * (size_t)h.m0, h.m0);
+                for (int lv = 1; lv <= levels[i]; ++lv)
+                    h.neighbors(i, lv, adju.data() + (upper_off[i] + (uint64_t)(lv - 1)) * h.m, h.m);
+            }
+        });
+    for (auto& th : pool)
+        th.join();
+    return upload_arrays(ix, n, h.viewed_vectors(), adj0.data(), adju.data(), upper_off.data(), levels.data());
 }
 
 rb::GraphView graph_view(rb_index* ix) {
@@ -1355,14 +1397,10 @@ std::string prepare_search(rb_index* ix, size_t k) {
     rbh::HostIndex& h = ix->host;
     if (!k)
         return "k must be positive";
-    if (h.viewing) {
-        // a viewed index can be searched only if its fingerprints are mapped: materialise it on the device once
-        return "rad_b200 cannot search a viewed index; load() it instead (view serves graph reads only)";
-    }
     std::string err = ensure_device(ix);
     if (!err.empty())
         return err;
-    return upload_graph(ix);
+    return h.viewing ? upload_view(ix) : upload_graph(ix);
 }
 
 }  // namespace
@@ -1696,7 +1734,7 @@ void rb_search(rb_index_t* ix, uint8_t const* queries, size_t nq, size_t stride,
         int32_t c = counts[q];
         counts_out[q] = c;
         for (int32_t j = 0; j < c; ++j) {
-            keys_out[q * k + j] = h.keys[slots[q * k + j]];
+            keys_out[q * k + j] = h.key_of(slots[q * k + j]);
             distances_out[q * k + j] = dists[q * k + j];
         }
     }

@@ -150,6 +150,19 @@ def test_structural_invariants_and_file_round_trip(tmp_path):
     q = synth.queries_from_db(db, 64, seed=3)
     a, b = ix.search(q, 10), loaded.search(q, 10)
     assert np.array_equal(a.keys, b.keys) and np.array_equal(a.distances, b.distances)
+    # a VIEWED index (mmap) is searched like the reference searches one (index_dense.hpp:1267-1415): graph and
+    # fingerprints come from the mapping; its graph reads keep working, adding to it does not
+    viewed = Index(ndim=1024, connectivity=m, path=path, view=True)
+    c = viewed.search(q, 10)
+    assert np.array_equal(a.keys, c.keys) and np.array_equal(a.distances, c.distances)
+    e1, e2 = ix.search(q, 10, exact=True), viewed.search(q, 10, exact=True)
+    assert np.array_equal(e1.keys, e2.keys) and np.array_equal(e1.distances.view(np.uint32), e2.distances.view(np.uint32))
+    assert np.array_equal(viewed.get_neighbors(17, 0), ix.get_neighbors(17, 0))
+    with pytest.raises(Exception):
+        viewed.add(np.array([5], dtype=np.uint64), db[:1])
+    bare = Index(ndim=1024, connectivity=m, path=path, view=True, exclude_vectors=True)
+    with pytest.raises(Exception):
+        bare.search(q, 10)
     with pytest.raises(ValueError):
         ix.get_neighbors(n, 0)
     with pytest.raises(ValueError):
