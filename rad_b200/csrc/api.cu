@@ -1156,6 +1156,18 @@ int exact_kernel_override() {
            : std::strcmp(e, "i8ts") == 0 ? 4 : 0;
 }
 
+// SMs of the current device (148 on a B200; the same figure when no device is visible, so that workspace sizes can
+// still be asked for)
+uint64_t current_sm_count() {
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        sms <= 0) {
+        cudaGetLastError();
+        return 148;
+    }
+    return (uint64_t)sms;
+}
+
 ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     ExactPlan p;
     const int forced = exact_kernel_override();
@@ -1167,7 +1179,8 @@ ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     p.pair = forced == 3 || (forced == 0 && p.tensor && RB_I8_PAIR_DEFAULT && nq > (uint64_t)rb::kTQ);
     p.ts = forced == 4 || (forced == 0 && p.tensor && !p.pair && RB_I8_TS_DEFAULT);
     const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.tensor ? rb::kTD : rb::kXD;
-    const uint64_t resident = p.tensor ? 148 : 296;  // CTAs resident on the 148 SMs
+    const uint64_t sms = current_sm_count();
+    const uint64_t resident = p.tensor ? sms : 2 * sms;  // resident CTAs: one (tensor kernel) or two (POPC kernel) per SM
     uint64_t qtiles = std::max<uint64_t>(1, (nq + tq - 1) / tq);
     if (p.pair)
         qtiles = (qtiles + 1) & ~(uint64_t)1;
