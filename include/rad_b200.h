@@ -204,6 +204,11 @@ RB_EXPORT void rb_copy_vectors_device(rb_index_t* index, uint64_t first, uint64_
 RB_EXPORT void rb_stitch_device(rb_index_t* index, uint64_t first, uint64_t count, uint64_t slot_base,
                                 void const* d_cand_slots, void const* d_cand_vectors, uint32_t cands, void* d_rows_out,
                                 rb_error_t* error);
+/* destination (EMPTY, created with connectivity = connectivity_base = the source's connectivity) becomes the sub-index
+ * of `source` over its nodes of level >= 1, one level down: graph level l + 1 of the source is level l of the
+ * destination, slots renumbered in ascending source order, fingerprints copied -- all on the device.  The upper levels
+ * of the stitch start from the links the build already made (index.hpp:2734-2834 builds every level in the one add). */
+RB_EXPORT void rb_extract_level(rb_index_t* source, rb_index_t* destination, rb_error_t* error);
 /* replace the graph of `index` by one assembled elsewhere: host arrays keys u64[n], levels i16[n], adj0 u32[n x 2M],
  * adj_upper u32[sum(levels) x M] (a node's rows consecutive, level 1 first), vectors u8[n x dimensions/8] or NULL,
  * entry = a node of the top level.  Afterwards the index saves / serves / searches like one built in one piece. */

@@ -86,6 +86,7 @@ SIGNATURES = {
     "rb_merge_topk_device": (None, [C.c_void_p, C.c_uint32, C.c_uint64, C.c_uint32, C.c_void_p, C.c_size_t, _ERR]),
     "rb_unpack_topk_device": (None, [C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_size_t, _ERR]),
+    "rb_extract_level": (None, [C.c_void_p, C.c_void_p, _ERR]),
     "rb_dedup_workspace_bytes": (C.c_size_t, [C.c_uint64]),
     "rb_dedup_device": (None, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, _ERR]),
     "rb_popcounts_device": (None, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t, _ERR]),

@@ -1662,6 +1662,97 @@ void rb_import_graph(rb_index_t* ix, uint64_t const* keys, int16_t const* levels
     ix->last = rb_counters_t{};
 }
 
+void rb_extract_level(rb_index_t* src, rb_index_t* dst, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    rbh::HostIndex& hs = src->host;
+    rbh::HostIndex& hd = dst->host;
+    if (hd.viewing || hd.size())
+        RB_FAIL("rb_extract_level fills an empty index");
+    if (hs.viewing)
+        RB_FAIL("rb_extract_level reads a built or loaded index, not a view");
+    if (hd.m != hs.m || hd.m0 != hs.m || hd.ndim != hs.ndim)
+        RB_FAIL("the destination needs the source's connectivity as connectivity AND connectivity_base, and its dimensions");
+    std::string err = prepare_search(src, 1);
+    if (!err.empty())
+        RB_FAIL(err);
+    dst->opts.device = src->dev.device;
+    if (!(err = ensure_device(dst)).empty())
+        RB_FAIL(err);
+    const size_t n = hs.keys.size();
+    std::vector<uint32_t> slots, table(n, RB_EMPTY);
+    for (size_t i = 0; i < n; ++i)
+        if (hs.levels[i] >= 1) {
+            table[i] = (uint32_t)slots.size();
+            slots.push_back((uint32_t)i);
+        }
+    const size_t cnt = slots.size();
+    if (!cnt)
+        return;
+    std::vector<int16_t> lv(cnt);
+    std::vector<uint64_t> keys(cnt);
+    std::vector<uint32_t> off32(cnt);
+    std::vector<int8_t> lv8(cnt);
+    uint64_t upper = 0;
+    for (size_t i = 0; i < cnt; ++i) {
+        lv[i] = (int16_t)(hs.levels[slots[i]] - 1);
+        lv8[i] = (int8_t)lv[i];
+        keys[i] = i;
+        off32[i] = (uint32_t)upper;
+        upper += (uint64_t)lv[i];
+    }
+    if (!(err = ensure_capacity(dst, cnt, upper)).empty())
+        RB_FAIL(err);
+    DeviceState& d = dst->dev;
+    uint32_t *d_slots = nullptr, *d_table = nullptr;
+    cudaError_t e = cudaMalloc(&d_slots, cnt * 4);
+    if (e == cudaSuccess)
+        e = cudaMalloc(&d_table, n * 4);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(d_slots, slots.data(), cnt * 4, cudaMemcpyHostToDevice, d.stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(d_table, table.data(), n * 4, cudaMemcpyHostToDevice, d.stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(d.upper_off, off32.data(), cnt * 4, cudaMemcpyHostToDevice, d.stream);
+    if (e == cudaSuccess)
+        e = cudaMemcpyAsync(d.levels, lv8.data(), cnt, cudaMemcpyHostToDevice, d.stream);
+    if (e == cudaSuccess) {
+        rb::ExtractParams ep;
+        ep.src = graph_view(src);
+        ep.dst = graph_view(dst);
+        ep.dst_fp = d.fp;
+        ep.src_slots = d_slots;
+        ep.table = d_table;
+        ep.dst_levels = d.levels;
+        ep.count = (uint32_t)cnt;
+        const unsigned grid = (unsigned)std::min<size_t>((cnt * 32 + 255) / 256, (size_t)d.sm_count * 16);
+        rb::extract_level_kernel<<<grid, 256, 0, d.stream>>>(ep);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(d.stream);
+    cudaFree(d_slots);
+    cudaFree(d_table);
+    if (e != cudaSuccess)
+        RB_FAIL(std::string("CUDA error in extract_level: ") + cudaGetErrorString(e));
+    // host bookkeeping of the new index (the adjacency stays on the device until rb_sync_host)
+    hd.keys = keys;
+    hd.levels = lv;
+    hd.upper_off.assign(cnt + 1, 0);
+    for (size_t i = 0; i < cnt; ++i)
+        hd.upper_off[i + 1] = hd.upper_off[i] + (uint64_t)lv[i];
+    hd.max_level = hs.max_level - 1;
+    hd.entry = table[hs.entry];
+    hd.note_new_keys(keys.data(), cnt);
+    hd.note_new_levels(0, lv.data(), cnt);
+    hd.invalidate_level_edges();
+    d.rows = cnt;
+    d.upper_rows = upper;
+    dst->device_graph_valid = true;
+    dst->host_graph_valid = false;
+    dst->last = rb_counters_t{};
+}
+
 void rb_clear(rb_index_t* ix, rb_error_t* error) {
     if (error)
         *error = nullptr;

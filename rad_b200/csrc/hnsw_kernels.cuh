@@ -1175,6 +1175,48 @@ __global__ void __launch_bounds__(256) gather_rows_kernel(const uint4* __restric
     }
 }
 
+// ------------------------------------------------------------------------------------------------ level extraction
+// dst = the sub-index of src over src's nodes of level >= 1, ONE LEVEL DOWN: graph level l + 1 of src becomes level l of
+// dst (its level 0 is M wide), slots renumbered by `table` (src slot -> dst slot).  The upper levels of the cross-shard
+// stitch start from these links -- the ones the build already made -- instead of a second build.  One warp per node.
+struct ExtractParams {
+    GraphView src;
+    GraphView dst;              // dst.m0 == dst.m == src.m
+    uint4* dst_fp;
+    const uint32_t* src_slots;  // [count] ascending
+    const uint32_t* table;      // [src rows]
+    const int8_t* dst_levels;   // [count] = src level - 1
+    uint32_t count;
+};
+
+__global__ void __launch_bounds__(256) extract_level_kernel(ExtractParams p) {
+    const int lane = threadIdx.x & 31;
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < p.count; i += (gridDim.x * blockDim.x) >> 5) {
+        const uint32_t s = __ldg(p.src_slots + i);
+        if (lane < 8)
+            p.dst_fp[(size_t)i * 8 + lane] = load_slice(p.src.fp, s, lane);
+        const int lv = p.dst_levels[i];
+        const size_t src_row0 = (size_t)__ldg(p.src.upper_off + s);
+        const size_t dst_row0 = lv ? (size_t)__ldg(p.dst.upper_off + i) : 0;
+        for (int l = 0; l <= lv; ++l) {
+            if ((uint32_t)lane < p.src.m) {
+                const size_t from = (src_row0 + (uint32_t)l) * p.src.m + lane;
+                const uint32_t v = p.src.adju[from];
+                const uint32_t w = v == RB_EMPTY ? RB_EMPTY : __ldg(p.table + v);
+                const uint16_t pc = p.src.pcu[from];
+                if (l == 0) {
+                    p.dst.adj0[(size_t)i * p.dst.m0 + lane] = w;
+                    p.dst.pc0[(size_t)i * p.dst.m0 + lane] = pc;
+                } else {
+                    const size_t to = (dst_row0 + (uint32_t)(l - 1)) * p.dst.m + lane;
+                    p.dst.adju[to] = w;
+                    p.dst.pcu[to] = pc;
+                }
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ level statistics
 // Edges per level of the whole graph (index.hpp:3147-3179 counts them by walking every node on the host): counted here,
 // where the adjacency was produced, and handed to the host with it at rb_sync_host.  One thread per node.

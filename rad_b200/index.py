@@ -611,6 +611,13 @@ class Index:
                                            C.byref(err))
         self._check(err)
 
+    def extract_upper_levels(self, source: "Index") -> None:
+        """This EMPTY index (created with ``_connectivity_base=connectivity``) becomes ``source``'s nodes of level >= 1,
+        one level down, with the links the build already gave them (``rb_extract_level``; device to device)."""
+        err = C.c_char_p()
+        self._lib.rb_extract_level(source._handle(), self._handle(), C.byref(err))
+        self._check(err)
+
     def import_graph(self, keys, levels, adj0, adj_upper, vectors, entry: int) -> None:
         """Replace the graph by one assembled elsewhere (global slots): see ``rb_import_graph``."""
         keys = np.ascontiguousarray(keys, dtype=np.uint64)

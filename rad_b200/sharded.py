@@ -527,7 +527,7 @@ def _stitch_rows(shard, slot_base: int, comm, batch: int, kr: int, efm: int):
 
 def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 65536,
                        k_remote: int | None = None, ef_merge: int | None = None, timings: dict | None = None,
-                       comm=None, assemble: bool = True, gather_below: int = 262144):
+                       comm=None, assemble: bool = True, gather_below: int = 262144, rebuild_upper: bool = False):
     """ONE HNSW graph with global slots from the sub-graphs every rank built over its own row shard (SURVEY.md §8e
     row 3).  Collective: every rank calls it with its ``DeviceShard`` and the global slot of its first row; shards
     are contiguous and ordered by rank.
@@ -536,9 +536,11 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
     fingerprints (NCCL); every rank answers the other ranks' rows from its own graph (``k_remote`` nearest at ef
     ``ef_merge``) and sends the answers WITH their fingerprints back (all-to-all); every rank prunes own links + remote
     candidates with the reference's heuristic into rows of global slots (``rb_stitch_device``).
-    LEVEL d >= 1 -- the same, recursively: every rank builds a sub-index over ITS nodes with level >= d, one level down
-    (its level 0 = graph level d, rows M wide), and those sub-indexes are stitched like level 0; 1/M of the work of the
-    level below, on all GPUs at once.  Once at most ``gather_below`` nodes remain in total they are gathered on rank 0
+    LEVEL d >= 1 -- the same, recursively: every rank takes the sub-index of ITS nodes with level >= d, one level down
+    (its level 0 = graph level d, rows M wide) -- the links its own build already made for that level
+    (``rb_extract_level``; ``rebuild_upper=True`` builds it afresh instead, the first form of this code, 1 s slower per
+    10 M rows) -- and those sub-indexes are stitched like level 0; 1/M of the work of the level below, on all GPUs at
+    once.  Once at most ``gather_below`` nodes remain in total they are gathered on rank 0
     and all remaining levels are built there as one graph.
 
     Returns on rank 0 ``dict(levels, adj0, adj_upper, entry, max_level)`` (host arrays, global slots), ``None`` on the
@@ -580,6 +582,7 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
     # ---- upper levels
     lv = np.asarray(shard.levels(), dtype=np.int16)
     pieces, piece_counts, keep, top, top_built = [], [], [], None, False
+    detail = []  # per stitched upper level: nodes in total, seconds of this rank's sub-index build and of its stitch
     cur, cur_lv = shard, lv
     cur_glob = torch.arange(n_local, dtype=torch.int64, device=dev) + int(slot_base)
     depth = 0
@@ -593,27 +596,42 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
         idx32 = torch.from_numpy(up_idx.astype(np.int32)).to(dev)
         up_glob = cur_glob[idx32.long()]
         sub_lv = (cur_lv[up_idx] - 1).astype(np.int16)
-        fp = cur.gather_vectors(idx32) if len(up_idx) else torch.zeros((0, 128), dtype=torch.uint8, device=dev)
         cap = max(max(n_up), 1)
-        if world == 1 or total <= gather_below:
+        gather_top = world == 1 or total <= gather_below
+        fp = None
+        if gather_top or rebuild_upper:
+            fp = cur.gather_vectors(idx32) if len(up_idx) else torch.zeros((0, 128), dtype=torch.uint8, device=dev)
+        if gather_top:
             top_built = True  # (on every rank: the collectives below must stay in step)
             g_glob = comm.gather0(padded(up_glob, cap, -1))
             g_fp = comm.gather0(padded(fp, cap, 0))
             g_lv = comm.gather0(padded(torch.from_numpy(sub_lv).to(dev), cap, 0))
             if rank == 0:
+                t_a = time.perf_counter()
                 t_glob = torch.cat([g_glob[h][:n_up[h]] for h in range(world)]).cpu().numpy()
                 t_lv = torch.cat([g_lv[h][:n_up[h]] for h in range(world)]).cpu().numpy().astype(np.int16)
                 t_fp = torch.cat([g_fp[h][:n_up[h]].to(dev) for h in range(world)])
                 a0, au, sub_entry, _ = shard.build_upper(t_fp, t_lv, expansion_add)
                 top = dict(level=depth, slots=t_glob, sub_levels=t_lv, a0=a0, au=au, entry=int(t_glob[sub_entry]))
+                detail.append(dict(level=depth, nodes=total, build_s=time.perf_counter() - t_a, stitch_s=0.0,
+                                   gathered_on_rank_0=True))
             break
+        t_a = time.perf_counter()
         sub = Index(ndim=shard.index.ndim, connectivity=m, expansion_add=expansion_add,
                     device=dev.index if dev.index is not None else -1, _connectivity_base=m)
         if len(up_idx):
             shard._settle()
-            sub.add_device(None, fp.data_ptr(), len(up_idx), levels=sub_lv)
+            if rebuild_upper:
+                sub.add_device(None, fp.data_ptr(), len(up_idx), levels=sub_lv)
+            else:
+                sub.extract_upper_levels(cur.index)
+                assert len(sub) == len(up_idx)
         ushard = DeviceShard(sub, dev)
+        sync()
+        t_b = time.perf_counter()
         rows_u, _ = _stitch_rows(ushard, int(sum(n_up[:rank])), comm, batch, kr, efm)
+        sync()
+        detail.append(dict(level=depth, nodes=total, build_s=t_b - t_a, stitch_s=time.perf_counter() - t_b))
         # this level's own numbering (rank-major, ascending slot) -> global slots
         allg = comm.all_gather(padded(up_glob, cap, -1))
         table = torch.cat([allg[h, :n_up[h]] for h in range(world)] + [torch.tensor([-1], dtype=torch.int64, device=dev)])
@@ -634,6 +652,7 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
         timings["stitch_s"] = t_stitch - t_start
         timings["upper_levels_s"] = t_upper - t_stitch
         timings["k_remote"], timings["ef_merge"], timings["stitched_levels"] = kr, efm, 1 + len(pieces)
+        timings["upper_detail"] = detail
     if not assemble:
         out = dict(rows=rows0, upper=pieces)
         if rank == 0:

@@ -147,3 +147,47 @@ def test_stitched_graph_is_one_valid_graph_with_single_graph_recall(kind, shards
         ref.expansion_search = 64
         theirs = _recall(ref.search(q, 10).distances, exact.distances)
         assert theirs >= report[64][0] - 0.01  # the reference's own search walks the stitched graph just as well
+
+
+def test_extracted_upper_levels_are_the_links_of_the_build():
+    """rb_extract_level: the sub-index of the nodes of level >= 1, one level down, equals a numpy remap of the source's
+    own upper-level rows; it answers searches and extracts again (the recursion of the upper-level stitch)."""
+    n, m = 40000, 8
+    db = synth.named_set("dense", n, seed=6)
+    src = Index(ndim=1024, connectivity=m, expansion_add=64, expansion_search=64)
+    src.add(np.arange(n, dtype=np.uint64), db)
+    lv = np.asarray(src.levels, dtype=np.int64)
+    _, au = src._debug_adjacency()
+    upper_off = np.concatenate([[0], np.cumsum(lv)])
+    for depth in range(2):
+        sub = Index(ndim=1024, connectivity=m, expansion_add=64, expansion_search=64, _connectivity_base=m)
+        sub.extract_upper_levels(src)
+        up = np.flatnonzero(lv >= 1)
+        assert len(sub) == len(up) and sub.max_level == src.max_level - 1
+        assert np.array_equal(np.asarray(sub.levels, dtype=np.int64), lv[up] - 1)
+        table = np.full(len(lv) + 1, EMPTY, dtype=np.uint32)
+        table[up] = np.arange(len(up), dtype=np.uint32)
+
+        def remap(rows):
+            return table[np.where(rows == EMPTY, len(lv), rows).astype(np.int64)]
+
+        sub.sync_host()
+        s0, su = sub._debug_adjacency()
+        assert s0.shape == (len(up), m)
+        assert np.array_equal(s0, remap(au[upper_off[up]]))
+        sub_off = np.concatenate([[0], np.cumsum(lv[up] - 1)])
+        deeper = np.flatnonzero(lv[up] >= 2)
+        assert np.array_equal(su[sub_off[deeper]], remap(au[upper_off[up[deeper]] + 1]))
+        assert int(sub.entry_slot) == int(table[src.entry_slot])
+        vec = sub.get_vectors(np.arange(0, len(up), 97, dtype=np.uint64)) if hasattr(sub, "get_vectors") else None
+        q = np.ascontiguousarray(db[up[::53]][:64]) if depth == 0 else None
+        if q is not None:
+            got = sub.search(q, 5, exact=True)  # keys of the sub-index are its own slots
+            slots, dists, _ = O.exact_search(np.ascontiguousarray(db[up]), q, 5)
+            assert np.array_equal(got.keys, slots) and np.array_equal(got.distances.view(np.uint32), dists.view(np.uint32))
+            approx = sub.search(q, 5)
+            assert _recall(approx.distances, dists, 5) > 0.9
+        del vec
+        # once more, from the extracted index
+        db, src, lv, au = db[up], sub, lv[up] - 1, su
+        upper_off = np.concatenate([[0], np.cumsum(lv)])
