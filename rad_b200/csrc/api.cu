@@ -24,6 +24,7 @@
 #include "../../include/rad_b200.h"
 #include "exact_kernels.cuh"
 #include "exact_i8_kernels.cuh"
+#include "exact_f4_kernels.cuh"
 #include "hnsw_kernels.cuh"
 #include "host_index.hpp"
 #include "ingest_kernels.cuh"
@@ -178,6 +179,8 @@ struct rb_index {
 };
 
 namespace {
+
+int exact_kernel_override();  // RB_EXACT_KERNEL (defined with plan_exact)
 
 std::string ensure_device(rb_index* ix) {
     DeviceState& d = ix->dev;
@@ -535,6 +538,8 @@ std::string configure_exact_kernels() {
                                  (int)rb::kTensorSmemBytes));
     RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)rb::kTensorSmemBytes));
+    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_f4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)rb::kF4SmemBytes));
     if (dev >= 0 && dev < 64)
         configured[dev] = true;
     return {};
@@ -830,7 +835,11 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
                     ep.tri_off[l] = ip.level_off[l];
                 }
                 dim3 grid((unsigned)((b.size + rb::kTQ - 1) / rb::kTQ), b.levels);
-                rb::exact_topk_i8_kernel_t<0><<<grid, rb::kTThreads, rb::kTensorSmemBytes, d.stream>>>(ep);
+                const int forced_kernel = exact_kernel_override();  // (the FP4 kernel has no cycle counters)
+                if (!tile_debug && (forced_kernel == 0 || forced_kernel == 5))
+                    rb::exact_topk_f4_kernel<<<grid, rb::kFThreads, rb::kF4SmemBytes, d.stream>>>(ep);
+                else
+                    rb::exact_topk_i8_kernel_t<0><<<grid, rb::kTThreads, rb::kTensorSmemBytes, d.stream>>>(ep);
                 ++launches;
                 if (tile_debug) {
                     unsigned long long hh[32];
@@ -1141,19 +1150,20 @@ struct ExactPlan {
     bool tensor;  // tcgen05 int8 kernel (128-query tiles, 256-row stages) instead of the POPC kernel (64 x 64)
     bool pair;    // ... in its CTA-pair form (exact_topk_i8_kernel_t<1>)
     bool ts;      // ... with the query operand in tensor memory (exact_topk_i8_kernel_t<2>)
+    bool f4;      // the FP4 tensor-core kernel (exact_topk_f4_kernel: kind::mxf4, 224-row tiles) -- the default tensor path
     uint32_t chunks;
     uint64_t chunk_rows;
     size_t keys_bytes, iu_bytes;  // iu_bytes includes the per-query bound words at bounds_off
     size_t bounds_off;            // u64[Q] shared k-th-distance bounds (tensor-core kernels), from the workspace start
 };
 
-// RB_EXACT_KERNEL=popc|i8|i8x2|i8ts forces one of the bit-identical kernels (tests, profiling)
+// RB_EXACT_KERNEL=popc|f4|i8|i8x2|i8ts forces one of the bit-identical kernels (tests, profiling)
 int exact_kernel_override() {
     char const* e = std::getenv("RB_EXACT_KERNEL");  // read per call: tests flip it between calls
     if (!e)
         return 0;
     return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : std::strcmp(e, "i8x2") == 0 ? 3
-           : std::strcmp(e, "i8ts") == 0 ? 4 : 0;
+           : std::strcmp(e, "i8ts") == 0 ? 4 : std::strcmp(e, "f4") == 0 ? 5 : 0;
 }
 
 // SMs of the current device (148 on a B200; the same figure when no device is visible, so that workspace sizes can
@@ -1178,7 +1188,8 @@ ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     // CTA pairs (cta_group::2): two adjacent query tiles share every unpacked database tile
     p.pair = forced == 3 || (forced == 0 && p.tensor && RB_I8_PAIR_DEFAULT && nq > (uint64_t)rb::kTQ);
     p.ts = forced == 4 || (forced == 0 && p.tensor && !p.pair && RB_I8_TS_DEFAULT);
-    const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.tensor ? rb::kTD : rb::kXD;
+    p.f4 = forced == 5 || (forced == 0 && p.tensor && !p.pair && !p.ts);
+    const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.f4 ? rb::kFD : p.tensor ? rb::kTD : rb::kXD;
     const uint64_t sms = current_sm_count();
     const uint64_t resident = p.tensor ? sms : 2 * sms;  // resident CTAs: one (tensor kernel) or two (POPC kernel) per SM
     uint64_t qtiles = std::max<uint64_t>(1, (nq + tq - 1) / tq);
@@ -1277,7 +1288,9 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
         RB_CUDA(cudaLaunchKernelEx(&cfg, rb::exact_topk_i8_kernel_t<1>, ep));
     } else if (pl.tensor) {
         dim3 grid((unsigned)((nq + rb::kTQ - 1) / rb::kTQ), pl.chunks);  // query tiles fastest: CTAs resident
-        if (pl.ts)
+        if (pl.f4)
+            rb::exact_topk_f4_kernel<<<grid, rb::kFThreads, rb::kF4SmemBytes, stream>>>(ep);
+        else if (pl.ts)
             rb::exact_topk_i8_kernel_t<2><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);
         else
             rb::exact_topk_i8_kernel_t<0><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows

@@ -1,0 +1,455 @@
+// exact_f4_kernels.cuh -- exact Tanimoto top-k on the FP4 path of the 5th-generation tensor cores (tcgen05, sm_100a).
+//
+// Same contract and the same structure as exact_topk_i8_kernel_t<0> (exact_i8_kernels.cuh; replaces
+// index_gt::search_exact_, usearch/include/usearch/index.hpp:4222-4239, tie rule index.hpp:923-934), with the
+// intersection counts formed by `tcgen05.mma kind::mxf4.block_scale` instead of `kind::i8`:
+//     inter[q][d] = sum_k bit_k(q) * bit_k(d),   bits as e2m1 values, every block scale = 1.0 (ue8m0 127), f32 accumulate
+// An instruction covers K = 64 fingerprint bits at the cycles kind::i8 needs for 32 (scripts/mma_f4_microbench.cu:
+// 166.8 vs 166.0 cycles at M128 N256; sums of <= 1024 products of small powers of two are exact in f32), a fingerprint
+// unpacks to 512 bytes instead of 1024 (half the producers' stores, half the operand bytes through the shared-memory
+// port per pair), and the query operand shrinks to 64 KB, which pays for a 4-stage B ring: one whole database tile in
+// flight.  Tensor memory holds two accumulators AND the scale factors, so the tile is 224 rows wide (2 x 224 + 64 of
+// the 512 columns).
+//   unpack (any fixed bit -> K position works as long as both operands use it): a 32-bit word w becomes the four
+//   words of one 16-byte K piece, eight 4-bit elements each --
+//     database:  w & 0x11111111 (e2m1 0b0001 = 0.5), w & 0x22222222 (1.0), w & 0x44444444 (2.0), (w >> 3) & 0x11111111 (0.5)
+//     query:     the reciprocal values 2.0, 1.0, 0.5, 2.0 -- every matching bit contributes exactly 1.0
+// The epilogue's filter is the integer test of the other kernels carried out in f32 (all its terms stay below 2^24).
+// Results are bit-identical to exact_topk_kernel and exact_topk_i8_kernel_t (tests/test_gpu_exact.py runs every case
+// on all of them).
+#pragma once
+#include "exact_i8_kernels.cuh"
+
+namespace rb {
+
+constexpr int kFQ = 128;               // queries per CTA (UMMA M)
+constexpr int kFD = 224;               // database rows per tile (UMMA N)
+constexpr int kFPieces = 8;            // 16-byte K pieces (32 fingerprint bits each) per B stage
+constexpr int kFStages = 4;            // B ring: 4 stages = the 1024 bits of one tile
+constexpr int kFSteps = 32 / kFPieces; // stages per database tile
+constexpr int kFEpiWarps = 4, kFMmaWarp = 4, kFProdWarp0 = 5, kFProdWarps = kFD / 32;  // 7 producer warps
+constexpr int kFThreads = (kFEpiWarps + 1 + kFProdWarps) * 32;  // 384
+constexpr uint32_t kFSBO_A = 32 * kLBO;                  // A holds all 32 K pieces of a row group
+constexpr uint32_t kFSBO_B = kFPieces * kLBO;
+constexpr uint32_t kFASmemBytes = (kFQ / 8) * kFSBO_A;   // 65536
+constexpr uint32_t kFStageBytes = (kFD / 8) * kFSBO_B;   // 28672
+constexpr uint32_t kFSfColumn = 2 * kFD;                 // scale factors: TMEM columns [448, 512)
+
+struct F4SmemTail {
+    uint32_t pq[kFQ];
+    uint32_t pd[2][kFD];     // row popcounts (kTPadRow for padding rows)
+    float pdf[2][kFD];       // the same as f32, for the filter
+    uint4 thr[kFQ];
+    uint32_t queue[kFEpiWarps][kTQueueCap / kFEpiWarps];
+    uint32_t queue_count[kFEpiWarps];
+    uint32_t lnslot[kFQ][kTListK + 1];
+    uint32_t liu[kFQ][kTListK + 1];
+    uint32_t tmem_base;
+    unsigned long long full[kFStages], empty[kFStages], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
+};
+constexpr size_t kF4SmemBytes = kFASmemBytes + kFStages * kFStageBytes + sizeof(F4SmemTail) + 128;
+static_assert(kF4SmemBytes <= 232448, "227 KB of shared memory per CTA");
+
+// instruction descriptor of the block-scaled kinds (cute/arch/mma_sm100_desc.hpp: InstrDescriptorBlockScaled): a / b
+// format E2M1 = 1 at [7,10) / [10,13), both K-major, N >> 3 at [17,23), scale format UE8M0 = 1 at bit 23, M >> 4 at
+// [24,29), scale-factor ids 0, K = 64 (bit 31 clear)
+constexpr uint32_t kIdescF4 = (1u << 7) | (1u << 10) | ((uint32_t)(kFD >> 3) << 17) | (1u << 23) | ((uint32_t)(kFQ >> 4) << 24);
+
+__device__ __forceinline__ void tc_mma_f4(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t sfa,
+                                          uint32_t sfb, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(sfa), "r"(sfb)
+        : "memory");
+}
+__device__ __forceinline__ uint4 unpack_f4_db(uint32_t w) {
+    return make_uint4(w & 0x11111111u, w & 0x22222222u, w & 0x44444444u, (w >> 3) & 0x11111111u);
+}
+__device__ __forceinline__ uint4 unpack_f4_query(uint32_t w) {
+    return make_uint4((w & 0x11111111u) << 2, w & 0x22222222u, (w & 0x44444444u) >> 2, ((w >> 3) & 0x11111111u) << 2);
+}
+
+// grid = (query tiles of 128, database chunks) or, in the triangular form, (query tiles, levels); ExactParams as for
+// the other kernels with chunk_rows a multiple of kFD
+__global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams p) {
+    extern __shared__ __align__(1024) unsigned char raw[];
+    unsigned char* smem_a = raw;
+    unsigned char* smem_b = raw + kFASmemBytes;
+    F4SmemTail& s = *reinterpret_cast<F4SmemTail*>(raw + kFASmemBytes + kFStages * kFStageBytes);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool tri = p.tri != 0;
+    const uint32_t qcount = tri ? p.tri_cnt[blockIdx.y] : p.query_count;
+    const uint32_t q0 = (tri ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * kFQ;
+    if (tri && q0 >= qcount)
+        return;  // uniform: the launch is sized for the widest level
+    const uint32_t chunk = tri ? 0u : blockIdx.y;
+    const size_t out_base = tri ? (size_t)p.tri_off[blockIdx.y] : (size_t)chunk * p.query_count;
+    const size_t bound_base = tri ? (size_t)p.tri_off[blockIdx.y] : 0;
+    const uint64_t row_begin = (uint64_t)chunk * p.chunk_rows;
+    const uint64_t row_end = tri ? (qcount < q0 + kFQ - 1 ? qcount : q0 + kFQ - 1)
+                                 : (row_begin + p.chunk_rows < p.rows ? row_begin + p.chunk_rows : p.rows);
+    const uint64_t n_tiles = row_begin < row_end ? (row_end - row_begin + kFD - 1) / kFD : 0;
+
+    // ---- the CTA's partial lists start empty
+    {
+        uint32_t nq = q0 >= qcount ? 0u : qcount - q0 < (uint32_t)kFQ ? qcount - q0 : (uint32_t)kFQ;
+        size_t base = (out_base + q0) * p.k;
+        for (size_t i = tid; i < (size_t)nq * p.k; i += kFThreads)
+            p.partial_keys[base + i] = ~0ull;
+    }
+    if (n_tiles == 0)
+        return;  // uniform
+
+    // ---- query tile: popcounts, thresholds, and the resident unpacked A operand (one piece per 32-bit word)
+    for (int r = tid; r < kFQ; r += kFThreads) {
+        uint32_t q = q0 + r, pc = 0;
+        if (q < qcount)
+            for (int w = 0; w < 8; ++w)
+                pc += popc4(__ldg(p.queries + (size_t)q * 8 + w));
+        s.pq[r] = q < qcount ? pc : kXInvalid;
+        s.thr[r] = make_uint4(0, 1, 0, 2048);  // list not full: every valid row (|d| < 2048) passes, padding rows do not
+    }
+    {
+        const uint32_t* q32 = reinterpret_cast<const uint32_t*>(p.queries);
+        for (int idx = tid; idx < kFQ * 32; idx += kFThreads) {
+            int r = idx & (kFQ - 1), piece = idx >> 7;
+            uint32_t q = q0 + r;
+            uint32_t w = q < qcount ? __ldg(q32 + (size_t)q * 32 + piece) : 0u;
+            *reinterpret_cast<uint4*>(smem_a + (r >> 3) * kFSBO_A + piece * kLBO + (r & 7) * 16) = unpack_f4_query(w);
+        }
+    }
+    if (tid == 0) {
+        for (int i = 0; i < kFStages; ++i) {
+            mbar_init(&s.full[i], kFProdWarps);  // one arrival per producer warp
+            mbar_init(&s.empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&s.tmem_full[i], 1);
+            mbar_init(&s.tmem_empty[i], kFEpiWarps);
+            mbar_init(&s.pd_full[i], kFProdWarps);
+            mbar_init(&s.pd_empty[i], kFEpiWarps);
+        }
+        for (int i = 0; i < kFEpiWarps; ++i)
+            s.queue_count[i] = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == kFMmaWarp) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&s.tmem_base))
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    fence_proxy_async();  // the A operand was written through the generic proxy
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = s.tmem_base;
+    if (warp < kFEpiWarps) {
+        // every scale factor is 1.0: thread = TMEM lane, columns [448, 512) = 0x7F7F7F7F (ue8m0 127 in every byte, so the
+        // instruction reads 1.0 whatever the layout of the factors inside those columns)
+        const uint32_t one = 0x7F7F7F7Fu;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + kFSfColumn + (uint32_t)(h * 32);
+            asm volatile(
+                "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+                "{%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, "
+                "%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(taddr), "r"(one)
+                : "memory");
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+
+    if (warp >= kFProdWarp0) {
+        // ================================================================ producers: one database row per thread
+        const int pr = tid - kFProdWarp0 * 32;  // 0 .. 223
+        unsigned char* my_b = smem_b + (pr >> 3) * kFSBO_B + (pr & 7) * 16;
+        uint4 v[8];
+        {
+            const uint64_t row0 = row_begin + (n_tiles - 1) * kFD + pr;
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                v[c] = row0 < row_end ? __ldg(p.db + row0 * 8 + c) : make_uint4(0, 0, 0, 0);
+        }
+        for (uint64_t t = 0; t < n_tiles; ++t) {
+            const uint64_t tile = n_tiles - 1 - t;  // highest rows first (see exact_kernels.cuh)
+            const uint64_t row = row_begin + tile * kFD + pr;
+            uint4 vn[8];
+            {
+                const uint64_t rown = row - kFD;  // tile - 1 (only used when t + 1 < n_tiles; always < row_end then)
+                const bool more = t + 1 < n_tiles;
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+                    vn[c] = more ? __ldg(p.db + rown * 8 + c) : make_uint4(0, 0, 0, 0);
+            }
+            uint32_t pc = 0;
+#pragma unroll
+            for (int h = 0; h < kFSteps; ++h) {  // stage h of the tile = fingerprint words 8 h .. 8 h + 7 = uint4 2 h, 2 h + 1
+                pc += popc4(v[2 * h]) + popc4(v[2 * h + 1]);
+                const uint32_t w[8] = {v[2 * h].x, v[2 * h].y, v[2 * h].z, v[2 * h].w,
+                                       v[2 * h + 1].x, v[2 * h + 1].y, v[2 * h + 1].z, v[2 * h + 1].w};
+                const uint64_t g = t * kFSteps + h;
+                const int st = (int)(g % kFStages);
+                uint4 u[kFPieces];
+#pragma unroll
+                for (int j = 0; j < kFPieces; ++j)  // K piece 8 h + j  <->  A piece of the same index
+                    u[j] = unpack_f4_db(w[j]);
+                mbar_wait(&s.empty[st], (uint32_t)(((g / kFStages) & 1) ^ 1));
+                unsigned char* dst = my_b + st * kFStageBytes;
+#pragma unroll
+                for (int j = 0; j < kFPieces; ++j)
+                    *reinterpret_cast<uint4*>(dst + j * kLBO) = u[j];
+                fence_proxy_async();
+                __syncwarp();
+                if (lane == 0)
+                    mbar_arrive(&s.full[st]);
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c)
+                v[c] = vn[c];
+            const int a = (int)(t & 1);
+            mbar_wait(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));  // epilogue of tile t - 2 done with pd[a]
+            const uint32_t pdv = row < row_end ? pc : kTPadRow;
+            s.pd[a][pr] = pdv;
+            s.pdf[a][pr] = (float)pdv;
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&s.pd_full[a]);
+        }
+    } else if (warp == kFMmaWarp) {
+        // ================================================================ MMA issuer
+        const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), kLBO, kFSBO_A);
+        const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), kLBO, kFSBO_B);
+        const uint32_t sfa = tmem_base + kFSfColumn, sfb = tmem_base + kFSfColumn + 32;
+        for (uint64_t t = 0; t < n_tiles; ++t) {
+            const int a = (int)(t & 1);
+            mbar_wait(&s.tmem_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));
+            tc_fence_after();
+            for (int c = 0; c < kFSteps; ++c) {
+                const uint64_t g = t * kFSteps + c;
+                const int st = (int)(g % kFStages);
+                mbar_wait(&s.full[st], (uint32_t)((g / kFStages) & 1));
+                tc_fence_after();
+                if (lane == 0) {
+#pragma unroll
+                    for (int j = 0; j < kFPieces / 2; ++j) {
+                        // K = 64 elements per instruction = two 16-byte K pieces
+                        const uint64_t ad = a_desc0 + (uint64_t)(((c * kFPieces + j * 2) * kLBO) >> 4);
+                        const uint64_t bd = b_desc0 + (uint64_t)((st * kFStageBytes + j * 2 * kLBO) >> 4);
+                        tc_mma_f4(tmem_base + (uint32_t)a * kFD, ad, bd, kIdescF4, sfa, sfb, (uint32_t)((c | j) != 0));
+                    }
+                    tc_commit(&s.empty[st]);
+                    if (c == kFSteps - 1)
+                        tc_commit(&s.tmem_full[a]);
+                }
+                __syncwarp();
+            }
+        }
+    } else {
+        // ================================================================ epilogue: thread = one query of the tile
+        const int ql = warp * 32 + lane;
+        const uint32_t pqv = s.pq[ql];
+        const bool smem_lists = p.k <= (uint32_t)kTListK;
+        const bool share_bounds = smem_lists && p.bounds != nullptr;
+        const uint32_t kk = p.k;
+        uint32_t llen = 0, w_i = 0, w_u = 1, w_ns = 0, w_pos = 0, own_bits = 0xFFFFFFFFu;
+        for (uint64_t t = 0; t < n_tiles; ++t) {
+            const uint64_t tile = n_tiles - 1 - t;
+            const int a = (int)(t & 1);
+            const uint32_t acc_ph = (uint32_t)((t >> 1) & 1);
+            mbar_wait(&s.pd_full[a], acc_ph);
+            mbar_wait(&s.tmem_full[a], acc_ph);
+            tc_fence_after();
+            // shared bounds: see exact_topk_i8_kernel_t
+            if (share_bounds && pqv != kXInvalid) {
+                const unsigned long long g = __ldcg(p.bounds + bound_base + q0 + ql);
+                if (g != ~0ull && (llen < kk || (!tri && (uint32_t)(g >> 32) < own_bits))) {
+                    const uint32_t holder = (uint32_t)(g >> 23) & 0x1FFu;
+                    const uint32_t it_ = (uint32_t)(g >> 12) & 0x7FFu, ut = (uint32_t)g & 0xFFFu;
+                    s.thr[ql] = make_uint4(ut + it_, it_, it_ * pqv, chunk < holder ? 0u : 1u);
+                }
+            }
+            // 32-column blocks from the HIGHEST rows down
+            for (int b = kFD / 32 - 1; b >= 0; --b) {
+                uint32_t acc[32];  // f32 bit patterns of the counts
+                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * kFD + b * 32);
+                RB_TMEM_LD32(acc, taddr);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (b == 0) {  // the accumulator stage is free as soon as the last block is in registers
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(&s.tmem_empty[a]);
+                }
+                // the integer filter in f32: the pair passes iff  dlt = (y |d| + B - w) - i A  is negative; every term is
+                // an integer below 2^24, so the f32 arithmetic is exact and +0 (not -0) stands for "equal"
+                uint32_t hm[4] = {0, 0, 0, 0};
+                {
+                    const uint4 th = s.thr[ql];
+                    const float neg_a = -(float)th.x, bw = (float)(int)(th.z - th.w), y = (float)th.y;
+                    const float4* pd4 = reinterpret_cast<const float4*>(&s.pdf[a][b * 32]);
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) {
+                        const float4 pv = pd4[g];
+                        const float pdv[4] = {pv.x, pv.y, pv.z, pv.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float r1 = __fmaf_rn(y, pdv[e], bw);
+                            const float dlt = __fmaf_rn(__uint_as_float(acc[g * 4 + e]), neg_a, r1);
+                            hm[g >> 1] = __funnelshift_l(__float_as_uint(dlt), hm[g >> 1], 1);
+                        }
+                    }
+                }
+                const uint32_t any_hit = pqv == kXInvalid ? 0u : (hm[0] | hm[1] | hm[2] | hm[3]);
+                if (smem_lists) {
+                    if (any_hit) {
+                        // bit 8 r + 7 - j of `hits` <-> column 8 r + j of the block (exact_topk_i8_kernel_t has the notes)
+                        uint32_t hits = (hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0];
+                        uint32_t* ls = &s.lnslot[ql][0];
+                        uint32_t* li = &s.liu[ql][0];
+                        bool changed = false;
+#pragma unroll 1
+                        while (hits) {
+                            const uint32_t bit = 31u - (uint32_t)__clz((int)hits);
+                            hits &= ~(1u << bit);
+                            const uint32_t col = (bit & 24u) | (7u - (bit & 7u));
+                            const uint32_t iv = (uint32_t)__float2uint_rn(__uint_as_float(select32(acc, col)));
+                            const uint32_t dl = (uint32_t)(b * 32) + col;
+                            const uint32_t pdv = s.pd[a][dl];
+                            if (pdv >= kTPadRow)  // a padding row can pass a non-strict bound with i_t = 0
+                                continue;
+                            const uint64_t row = row_begin + tile * kFD + dl;
+                            if (tri && row >= (uint64_t)q0 + (uint32_t)ql)
+                                continue;         // triangular form: only the rows in front of the query
+                            const uint32_t u = pqv + pdv - iv, uu = u ? u : 1u;  // u == 0: distance 1 = ratio 0
+                            const uint32_t ns = ~(uint32_t)(p.slot_base + row);
+                            if (llen == kk) {
+                                const uint32_t lhs = iv * w_u, rhs = w_i * uu;  // counts <= 1024, unions <= 2048
+                                if (lhs < rhs || (lhs == rhs && ns > w_ns))
+                                    continue;
+                                li[w_pos] = iv | (uu << 16);
+                                ls[w_pos] = ns;
+                                uint32_t ci = iv, cu = uu, cns = ns, cpos = w_pos;
+#pragma unroll 1
+                                for (uint32_t e0 = 0; e0 < kk; e0 += 4) {
+                                    uint32_t eiu[4], ens[4];
+#pragma unroll
+                                    for (uint32_t t4 = 0; t4 < 4; ++t4) {
+                                        eiu[t4] = li[e0 + t4];
+                                        ens[t4] = ls[e0 + t4];
+                                    }
+#pragma unroll
+                                    for (uint32_t t4 = 0; t4 < 4; ++t4) {
+                                        const uint32_t l2 = (eiu[t4] & 0xFFFFu) * cu, r2 = ci * (eiu[t4] >> 16);
+                                        if (e0 + t4 < kk && (l2 < r2 || (l2 == r2 && ens[t4] > cns)))
+                                            ci = eiu[t4] & 0xFFFFu, cu = eiu[t4] >> 16, cns = ens[t4], cpos = e0 + t4;
+                                    }
+                                }
+                                w_i = ci, w_u = cu, w_ns = cns, w_pos = cpos;
+                            } else {
+                                li[llen] = iv | (uu << 16);
+                                ls[llen] = ns;
+                                if (llen == 0 || iv * w_u < w_i * uu || (iv * w_u == w_i * uu && ns > w_ns))
+                                    w_i = iv, w_u = uu, w_ns = ns, w_pos = llen;
+                                ++llen;
+                            }
+                            changed = true;
+                        }
+                        if (changed && llen == kk) {
+                            s.thr[ql] = make_uint4(w_u + w_i, w_i, w_i * pqv, 0);
+                            if (share_bounds && !tri) {
+                                own_bits = exact_distance_bits(w_i, w_u);
+                                atomicMin(p.bounds + bound_base + q0 + ql,
+                                          ((unsigned long long)own_bits << 32) | ((unsigned long long)chunk << 23) |
+                                              ((unsigned long long)w_i << 12) | w_u);
+                            }
+                        }
+                    }
+                } else if (__any_sync(RB_FULL_MASK, any_hit != 0)) {
+                    // k > kTListK: lists in global memory, warp-local slow path (rounds of 8 columns, highest rows first)
+                    const uint32_t hits = pqv == kXInvalid ? 0u : ((hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0]);
+#pragma unroll 1
+                    for (int r = 3; r >= 0; --r) {
+                        uint32_t hit = (hits >> (8 * r)) & 0xFFu;
+                        if (!__any_sync(RB_FULL_MASK, hit != 0))
+                            continue;
+                        while (hit) {
+                            const int j = 7 - (31 - __clz((int)hit));  // bit 7 - j <-> column 8 r + j
+                            hit &= ~(0x80u >> j);
+                            const uint32_t iv = (uint32_t)__float2uint_rn(__uint_as_float(select32(acc, (uint32_t)(r * 8 + j))));
+                            uint32_t at = atomicAdd(&s.queue_count[warp], 1u);
+                            s.queue[warp][at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + r * 8 + j) << 16) | iv;
+                        }
+                        __syncwarp();
+                        const uint32_t qn = s.queue_count[warp];
+                        for (uint32_t base = 0; base < qn; base += 32) {
+                            uint32_t e = base + lane < qn ? s.queue[warp][base + lane] : 0xFFFFFFFFu;
+                            for (uint32_t jj = 0; jj < 32 && base + jj < qn; ++jj) {
+                                uint32_t ev = __shfl_sync(RB_FULL_MASK, e, (int)jj);
+                                uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
+                                if (s.pd[a][dl] >= kTPadRow)
+                                    continue;
+                                if (tri && row_begin + tile * kFD + dl >= (uint64_t)q0 + eq)
+                                    continue;
+                                uint32_t u = s.pq[eq] + s.pd[a][dl] - i;
+                                uint32_t slot = (uint32_t)(p.slot_base + row_begin + tile * kFD + dl);
+                                uint64_t key = ((uint64_t)exact_distance_bits(i, u) << 32) | (uint32_t)~slot;
+                                const size_t off = (out_base + q0 + eq) * p.k;
+                                uint64_t* lk = p.partial_keys + off;
+                                uint32_t* li = p.partial_iu + off;
+                                glist_insert(lk, li, p.k, key, i | ((u ? u : 1u) << 16));
+                                if (lk[p.k - 1] != ~0ull) {
+                                    uint32_t iu = li[p.k - 1];
+                                    uint32_t it_ = iu & 0xFFFFu, ut = iu >> 16;
+                                    if (lane == 0)
+                                        s.thr[eq] = make_uint4(ut + it_, it_, it_ * s.pq[eq], 0);
+                                }
+                                __syncwarp();
+                            }
+                        }
+                        if (lane == 0)
+                            s.queue_count[warp] = 0;
+                        __syncwarp();
+                    }
+                }
+            }
+            if (lane == 0)
+                mbar_arrive(&s.pd_empty[a]);
+        }
+        if (smem_lists && pqv != kXInvalid) {  // publish this query's partial list: sorted, reference-exact bits at last
+            size_t off = (out_base + q0 + ql) * p.k;
+            uint32_t* ls = &s.lnslot[ql][0];
+            uint32_t* li = &s.liu[ql][0];
+            for (uint32_t j = 1; j < llen; ++j) {  // insertion sort, closest first
+                const uint32_t eiu = li[j], ens = ls[j];
+                uint32_t pos = j;
+                while (pos > 0) {
+                    const uint32_t piu = li[pos - 1], pns = ls[pos - 1];
+                    const uint32_t lhs = (eiu & 0xFFFFu) * (piu >> 16), rhs = (piu & 0xFFFFu) * (eiu >> 16);
+                    if (!(lhs > rhs || (lhs == rhs && ens < pns)))
+                        break;
+                    li[pos] = piu;
+                    ls[pos] = pns;
+                    --pos;
+                }
+                li[pos] = eiu;
+                ls[pos] = ens;
+            }
+            for (uint32_t j = 0; j < kk; ++j) {
+                const uint32_t eiu = li[j];
+                p.partial_keys[off + j] =
+                    j < llen ? (((unsigned long long)exact_distance_bits(eiu & 0xFFFFu, eiu >> 16) << 32) | ls[j]) : ~0ull;
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == kFMmaWarp)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+}
+
+}  // namespace rb

@@ -14,7 +14,7 @@ from rad_b200.index import Index
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["popc", "i8", "i8x2", "i8ts"])
+@pytest.fixture(autouse=True, params=["popc", "f4", "i8", "i8x2", "i8ts"])
 def exact_kernel(request, monkeypatch):
     """Every test of this module runs against ALL exact-search kernels: the POPC-pipe kernel, the tcgen05 int8
     tensor-core kernel, its CTA-pair (cta_group::2) form and its form with the query operand in tensor memory
