@@ -27,8 +27,12 @@ constexpr int kFD = 224;               // database rows per tile (UMMA N)
 constexpr int kFPieces = 8;            // 16-byte K pieces (32 fingerprint bits each) per B stage
 constexpr int kFStages = 4;            // B ring: 4 stages = the 1024 bits of one tile
 constexpr int kFSteps = 32 / kFPieces; // stages per database tile
-constexpr int kFEpiWarps = 4, kFMmaWarp = 4, kFProdWarp0 = 5, kFProdWarps = kFD / 32;  // 7 producer warps
-constexpr int kFThreads = (kFEpiWarps + 1 + kFProdWarps) * 32;  // 384
+// TWO epilogue groups of four warps (a warp reaches the TMEM lanes 32 (warp % 4) ..: warps 0-3 and 4-7 both cover all
+// 128 queries): group g owns accumulator stage g, i.e. the even / the odd tiles, so a tile's epilogue may take as long as
+// the MMAs of two tiles.  (With four warps the epilogue, 6.6 k cycles per tile, was what bounded the FP4 kernel.)
+constexpr int kFEpiGroups = 2, kFEpiWarps = 4 * kFEpiGroups, kFMmaWarp = kFEpiWarps, kFProdWarp0 = kFMmaWarp + 1;
+constexpr int kFProdWarps = kFD / 32;                            // 7 producer warps
+constexpr int kFThreads = (kFEpiWarps + 1 + kFProdWarps) * 32;  // 512
 constexpr uint32_t kFSBO_A = 32 * kLBO;                  // A holds all 32 K pieces of a row group
 constexpr uint32_t kFSBO_B = kFPieces * kLBO;
 constexpr uint32_t kFASmemBytes = (kFQ / 8) * kFSBO_A;   // 65536
@@ -39,14 +43,20 @@ struct F4SmemTail {
     uint32_t pq[kFQ];
     uint32_t pd[2][kFD];     // row popcounts (kTPadRow for padding rows)
     float pdf[2][kFD];       // the same as f32, for the filter
-    uint4 thr[kFQ];
-    uint32_t queue[kFEpiWarps][kTQueueCap / kFEpiWarps];
-    uint32_t queue_count[kFEpiWarps];
-    uint32_t lnslot[kFQ][kTListK + 1];
-    uint32_t liu[kFQ][kTListK + 1];
+    uint4 thr[kFEpiGroups][kFQ];       // the filter thresholds of thread (group, query): written by that thread only
+    uint32_t worst[kFEpiGroups][kFQ];  // i | u << 16 of the worst entry of that thread's FULL list, 0 before (read by
+                                       // the other group: the k-th best of the union is at least as good as either)
+    uint32_t llen[kFEpiGroups][kFQ];
+    uint32_t queue_count[4];
+    // per-(group, query) partial lists (k <= kTListK), merged when they are published; rows padded by one entry: the 32
+    // lanes of a warp touching the same column hit distinct banks.  For k > kTListK the lists live in global memory,
+    // group 0 works alone, and its survivor queues (4 x 256 words) lie over lnslot[1].
+    uint32_t lnslot[kFEpiGroups][kFQ][kTListK + 1];  // ~slot of each entry
+    uint32_t liu[kFEpiGroups][kFQ][kTListK + 1];     // i | u << 16 of each entry
     uint32_t tmem_base;
     unsigned long long full[kFStages], empty[kFStages], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
 };
+static_assert(sizeof(uint32_t) * kFQ * (kTListK + 1) >= sizeof(uint32_t) * kTQueueCap, "the queues fit over lnslot[1]");
 constexpr size_t kF4SmemBytes = kFASmemBytes + kFStages * kFStageBytes + sizeof(F4SmemTail) + 128;
 static_assert(kF4SmemBytes <= 232448, "227 KB of shared memory per CTA");
 
@@ -109,7 +119,11 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
             for (int w = 0; w < 8; ++w)
                 pc += popc4(__ldg(p.queries + (size_t)q * 8 + w));
         s.pq[r] = q < qcount ? pc : kXInvalid;
-        s.thr[r] = make_uint4(0, 1, 0, 2048);  // list not full: every valid row (|d| < 2048) passes, padding rows do not
+        for (int g = 0; g < kFEpiGroups; ++g) {
+            s.thr[g][r] = make_uint4(0, 1, 0, 2048);  // list not full: every valid row (|d| < 2048) passes, padding rows do not
+            s.worst[g][r] = 0;
+            s.llen[g][r] = 0;
+        }
     }
     {
         const uint32_t* q32 = reinterpret_cast<const uint32_t*>(p.queries);
@@ -127,11 +141,11 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s.tmem_full[i], 1);
-            mbar_init(&s.tmem_empty[i], kFEpiWarps);
+            mbar_init(&s.tmem_empty[i], 4);  // the four warps of the group that owns the stage
             mbar_init(&s.pd_full[i], kFProdWarps);
-            mbar_init(&s.pd_empty[i], kFEpiWarps);
+            mbar_init(&s.pd_empty[i], 4);
         }
-        for (int i = 0; i < kFEpiWarps; ++i)
+        for (int i = 0; i < 4; ++i)
             s.queue_count[i] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -145,7 +159,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = s.tmem_base;
-    if (warp < kFEpiWarps) {
+    if (warp < 4) {
         // every scale factor is 1.0: thread = TMEM lane, columns [448, 512) = 0x7F7F7F7F (ue8m0 127 in every byte, so the
         // instruction reads 1.0 whatever the layout of the factors inside those columns)
         const uint32_t one = 0x7F7F7F7Fu;
@@ -250,33 +264,56 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
             }
         }
     } else {
-        // ================================================================ epilogue: thread = one query of the tile
-        const int ql = warp * 32 + lane;
+        // ================================================================ epilogue: thread = (group, one query of the tile)
+        const int grp = warp >> 2, wq = warp & 3;  // group = accumulator stage = tile parity; wq = TMEM lane quadrant
+        const int ql = wq * 32 + lane;
         const uint32_t pqv = s.pq[ql];
         const bool smem_lists = p.k <= (uint32_t)kTListK;
         const bool share_bounds = smem_lists && p.bounds != nullptr;
+        const int groups = smem_lists ? kFEpiGroups : 1;  // k > kTListK: one list per query in global memory, group 0 alone
+        uint32_t (*queue)[kTQueueCap / 4] = reinterpret_cast<uint32_t (*)[kTQueueCap / 4]>(&s.lnslot[1][0][0]);
         const uint32_t kk = p.k;
-        uint32_t llen = 0, w_i = 0, w_u = 1, w_ns = 0, w_pos = 0, own_bits = 0xFFFFFFFFu;
-        for (uint64_t t = 0; t < n_tiles; ++t) {
+        // this thread's own list: length, and its worst entry once it is full (counts, ~slot, position)
+        uint32_t llen = 0, w_i = 0, w_u = 1, w_ns = 0, w_pos = 0;
+        for (uint64_t t = (uint64_t)grp; t < n_tiles && grp < groups; t += (uint64_t)groups) {
             const uint64_t tile = n_tiles - 1 - t;
-            const int a = (int)(t & 1);
+            const int a = (int)(t & 1);  // (== grp when both groups work)
             const uint32_t acc_ph = (uint32_t)((t >> 1) & 1);
             mbar_wait(&s.pd_full[a], acc_ph);
             mbar_wait(&s.tmem_full[a], acc_ph);
             tc_fence_after();
-            // shared bounds: see exact_topk_i8_kernel_t
-            if (share_bounds && pqv != kXInvalid) {
-                const unsigned long long g = __ldcg(p.bounds + bound_base + q0 + ql);
-                if (g != ~0ull && (llen < kk || (!tri && (uint32_t)(g >> 32) < own_bits))) {
-                    const uint32_t holder = (uint32_t)(g >> 23) & 0x1FFu;
-                    const uint32_t it_ = (uint32_t)(g >> 12) & 0x7FFu, ut = (uint32_t)g & 0xFFFu;
-                    s.thr[ql] = make_uint4(ut + it_, it_, it_ * pqv, chunk < holder ? 0u : 1u);
+            // The filter bound of this tile: the tightest of (1) the worst entry of this thread's own full list -- strict:
+            // its rows arrive from the highest slot down, so a row that merely ties loses; (2) the worst entry of the OTHER
+            // group's full list -- the k-th best of the union is at least as good as it; non-strict, that list's slots are
+            // interleaved with ours; (3) the bound word other CTAs published (see exact_topk_i8_kernel_t), strict for a
+            // lower chunk, non-strict for a higher one.  Ratios are compared by cross-multiplication (counts <= 1024,
+            // unions <= 2048).  Which survivors take the slow path depends on timing; the result does not.
+            if (pqv != kXInvalid) {
+                bool have = llen == kk;
+                uint32_t bi = w_i, bu = w_u, bw = 0;
+                if (groups > 1) {
+                    const uint32_t ow = *reinterpret_cast<volatile uint32_t*>(&s.worst[grp ^ 1][ql]);
+                    const uint32_t oi = ow & 0xFFFFu, ou = ow >> 16;
+                    if (ow && (!have || oi * bu > bi * ou))
+                        have = true, bi = oi, bu = ou, bw = 1;
                 }
+                if (share_bounds) {
+                    const unsigned long long g = __ldcg(p.bounds + bound_base + q0 + ql);
+                    if (g != ~0ull) {
+                        const uint32_t holder = (uint32_t)(g >> 23) & 0x1FFu;
+                        const uint32_t it_ = (uint32_t)(g >> 12) & 0x7FFu, ut = (uint32_t)g & 0xFFFu;
+                        // a seed of the triangular form only matters until a list is full (every entry passed it)
+                        if (tri ? llen < kk && !have : (!have || it_ * bu > bi * ut))
+                            have = true, bi = it_, bu = ut, bw = chunk < holder ? 0u : 1u;
+                    }
+                }
+                if (have)
+                    s.thr[grp][ql] = make_uint4(bu + bi, bi, bi * pqv, bw);
             }
             // 32-column blocks from the HIGHEST rows down
             for (int b = kFD / 32 - 1; b >= 0; --b) {
                 uint32_t acc[32];  // f32 bit patterns of the counts
-                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(a * kFD + b * 32);
+                const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * kFD + b * 32);
                 RB_TMEM_LD32(acc, taddr);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (b == 0) {  // the accumulator stage is free as soon as the last block is in registers
@@ -289,7 +326,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                 // an integer below 2^24, so the f32 arithmetic is exact and +0 (not -0) stands for "equal"
                 uint32_t hm[4] = {0, 0, 0, 0};
                 {
-                    const uint4 th = s.thr[ql];
+                    const uint4 th = s.thr[grp][ql];
                     const float neg_a = -(float)th.x, bw = (float)(int)(th.z - th.w), y = (float)th.y;
                     const float4* pd4 = reinterpret_cast<const float4*>(&s.pdf[a][b * 32]);
 #pragma unroll
@@ -309,8 +346,8 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                     if (any_hit) {
                         // bit 8 r + 7 - j of `hits` <-> column 8 r + j of the block (exact_topk_i8_kernel_t has the notes)
                         uint32_t hits = (hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0];
-                        uint32_t* ls = &s.lnslot[ql][0];
-                        uint32_t* li = &s.liu[ql][0];
+                        uint32_t* ls = &s.lnslot[grp][ql][0];
+                        uint32_t* li = &s.liu[grp][ql][0];
                         bool changed = false;
 #pragma unroll 1
                         while (hits) {
@@ -360,13 +397,15 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                             changed = true;
                         }
                         if (changed && llen == kk) {
-                            s.thr[ql] = make_uint4(w_u + w_i, w_i, w_i * pqv, 0);
-                            if (share_bounds && !tri) {
-                                own_bits = exact_distance_bits(w_i, w_u);
+                            // own list tighter: its worst entry becomes this thread's bound if it beats the one in use
+                            const uint4 cur = s.thr[grp][ql];  // (x - y, y) = (u, i) of the bound in use; y = 1, x = 0 before any
+                            if (cur.x == 0 || w_i * (cur.x - cur.y) >= cur.y * w_u)
+                                s.thr[grp][ql] = make_uint4(w_u + w_i, w_i, w_i * pqv, 0);
+                            *reinterpret_cast<volatile uint32_t*>(&s.worst[grp][ql]) = w_i | (w_u << 16);
+                            if (share_bounds && !tri)
                                 atomicMin(p.bounds + bound_base + q0 + ql,
-                                          ((unsigned long long)own_bits << 32) | ((unsigned long long)chunk << 23) |
-                                              ((unsigned long long)w_i << 12) | w_u);
-                            }
+                                          ((unsigned long long)exact_distance_bits(w_i, w_u) << 32) |
+                                              ((unsigned long long)chunk << 23) | ((unsigned long long)w_i << 12) | w_u);
                         }
                     }
                 } else if (__any_sync(RB_FULL_MASK, any_hit != 0)) {
@@ -381,13 +420,13 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                             const int j = 7 - (31 - __clz((int)hit));  // bit 7 - j <-> column 8 r + j
                             hit &= ~(0x80u >> j);
                             const uint32_t iv = (uint32_t)__float2uint_rn(__uint_as_float(select32(acc, (uint32_t)(r * 8 + j))));
-                            uint32_t at = atomicAdd(&s.queue_count[warp], 1u);
-                            s.queue[warp][at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + r * 8 + j) << 16) | iv;
+                            uint32_t at = atomicAdd(&s.queue_count[wq], 1u);
+                            queue[wq][at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + r * 8 + j) << 16) | iv;
                         }
                         __syncwarp();
-                        const uint32_t qn = s.queue_count[warp];
+                        const uint32_t qn = s.queue_count[wq];
                         for (uint32_t base = 0; base < qn; base += 32) {
-                            uint32_t e = base + lane < qn ? s.queue[warp][base + lane] : 0xFFFFFFFFu;
+                            uint32_t e = base + lane < qn ? queue[wq][base + lane] : 0xFFFFFFFFu;
                             for (uint32_t jj = 0; jj < 32 && base + jj < qn; ++jj) {
                                 uint32_t ev = __shfl_sync(RB_FULL_MASK, e, (int)jj);
                                 uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
@@ -406,13 +445,13 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                                     uint32_t iu = li[p.k - 1];
                                     uint32_t it_ = iu & 0xFFFFu, ut = iu >> 16;
                                     if (lane == 0)
-                                        s.thr[eq] = make_uint4(ut + it_, it_, it_ * s.pq[eq], 0);
+                                        s.thr[0][eq] = make_uint4(ut + it_, it_, it_ * s.pq[eq], 0);
                                 }
                                 __syncwarp();
                             }
                         }
                         if (lane == 0)
-                            s.queue_count[warp] = 0;
+                            s.queue_count[wq] = 0;
                         __syncwarp();
                     }
                 }
@@ -420,11 +459,12 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
             if (lane == 0)
                 mbar_arrive(&s.pd_empty[a]);
         }
-        if (smem_lists && pqv != kXInvalid) {  // publish this query's partial list: sorted, reference-exact bits at last
-            size_t off = (out_base + q0 + ql) * p.k;
-            uint32_t* ls = &s.lnslot[ql][0];
-            uint32_t* li = &s.liu[ql][0];
-            for (uint32_t j = 1; j < llen; ++j) {  // insertion sort, closest first
+        if (smem_lists) {
+            // publish: every thread sorts its own list (closest first), the two groups meet, group 0 merges the two
+            // sorted lists of its query and pays the f64 divide of the reference-exact bits for the k entries kept
+            uint32_t* ls = &s.lnslot[grp][ql][0];
+            uint32_t* li = &s.liu[grp][ql][0];
+            for (uint32_t j = 1; j < llen; ++j) {  // insertion sort
                 const uint32_t eiu = li[j], ens = ls[j];
                 uint32_t pos = j;
                 while (pos > 0) {
@@ -439,10 +479,32 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                 li[pos] = eiu;
                 ls[pos] = ens;
             }
-            for (uint32_t j = 0; j < kk; ++j) {
-                const uint32_t eiu = li[j];
-                p.partial_keys[off + j] =
-                    j < llen ? (((unsigned long long)exact_distance_bits(eiu & 0xFFFFu, eiu >> 16) << 32) | ls[j]) : ~0ull;
+            s.llen[grp][ql] = llen;
+            asm volatile("bar.sync 1, %0;" ::"r"(kFEpiWarps * 32) : "memory");  // the eight epilogue warps only
+            if (grp == 0 && pqv != kXInvalid) {
+                const size_t off = (out_base + q0 + ql) * p.k;
+                const uint32_t n0 = llen, n1 = s.llen[1][ql];
+                const uint32_t* ls1 = &s.lnslot[1][ql][0];
+                const uint32_t* li1 = &s.liu[1][ql][0];
+                uint32_t i0 = 0, i1 = 0;
+                for (uint32_t j = 0; j < kk; ++j) {
+                    uint32_t eiu = 0, ens = 0;
+                    bool any = false;
+                    if (i0 < n0 && i1 < n1) {
+                        const uint32_t a_iu = li[i0], b_iu = li1[i1];
+                        const uint32_t lhs = (a_iu & 0xFFFFu) * (b_iu >> 16), rhs = (b_iu & 0xFFFFu) * (a_iu >> 16);
+                        const bool first = lhs > rhs || (lhs == rhs && ls[i0] < ls1[i1]);  // closer, or the higher slot
+                        eiu = first ? a_iu : b_iu, ens = first ? ls[i0] : ls1[i1];
+                        i0 += first ? 1u : 0u, i1 += first ? 0u : 1u;
+                        any = true;
+                    } else if (i0 < n0) {
+                        eiu = li[i0], ens = ls[i0], ++i0, any = true;
+                    } else if (i1 < n1) {
+                        eiu = li1[i1], ens = ls1[i1], ++i1, any = true;
+                    }
+                    p.partial_keys[off + j] =
+                        any ? (((unsigned long long)exact_distance_bits(eiu & 0xFFFFu, eiu >> 16) << 32) | ens) : ~0ull;
+                }
             }
         }
     }
