@@ -28,8 +28,10 @@ constexpr int kFPieces = 8;            // 16-byte K pieces (32 fingerprint bits 
 constexpr int kFStages = 4;            // B ring: 4 stages = the 1024 bits of one tile
 constexpr int kFSteps = 32 / kFPieces; // stages per database tile
 // TWO epilogue groups of four warps (a warp reaches the TMEM lanes 32 (warp % 4) ..: warps 0-3 and 4-7 both cover all
-// 128 queries): group g owns accumulator stage g, i.e. the even / the odd tiles, so a tile's epilogue may take as long as
-// the MMAs of two tiles.  (With four warps the epilogue, 6.6 k cycles per tile, was what bounded the FP4 kernel.)
+// 128 queries).  Both groups work on EVERY tile, group 0 on its columns 112..223, group 1 on 0..111, so an accumulator
+// stage is held for half an epilogue and the epilogues of consecutive tiles run back to back.  (Four warps took 6.6 k
+// cycles per tile and bounded the kernel at 80 ms for 10 k x 10 M; the two groups on ALTERNATE tiles: 66 ms, bounded by
+// (MMA + epilogue) / 2 because an accumulator stayed occupied for a whole epilogue.)
 constexpr int kFEpiGroups = 2, kFEpiWarps = 4 * kFEpiGroups, kFMmaWarp = kFEpiWarps, kFProdWarp0 = kFMmaWarp + 1;
 constexpr int kFProdWarps = kFD / 32;                            // 7 producer warps
 constexpr int kFThreads = (kFEpiWarps + 1 + kFProdWarps) * 32;  // 512
@@ -38,11 +40,12 @@ constexpr uint32_t kFSBO_B = kFPieces * kLBO;
 constexpr uint32_t kFASmemBytes = (kFQ / 8) * kFSBO_A;   // 65536
 constexpr uint32_t kFStageBytes = (kFD / 8) * kFSBO_B;   // 28672
 constexpr uint32_t kFSfColumn = 2 * kFD;                 // scale factors: TMEM columns [448, 512)
+constexpr int kFPdRing = 4;                              // row-popcount side arrays in flight (tiles)
+constexpr int kFGroupCols = kFD / kFEpiGroups;           // 112 columns of a tile per epilogue group
 
 struct F4SmemTail {
     uint32_t pq[kFQ];
-    uint32_t pd[2][kFD];     // row popcounts (kTPadRow for padding rows)
-    float pdf[2][kFD];       // the same as f32, for the filter
+    float pdf[kFPdRing][kFD];  // row popcounts as f32 (kTPadRow for padding rows): the filter's operand; exact integers
     uint4 thr[kFEpiGroups][kFQ];       // the filter thresholds of thread (group, query): written by that thread only
     uint32_t worst[kFEpiGroups][kFQ];  // i | u << 16 of the worst entry of that thread's FULL list, 0 before (read by
                                        // the other group: the k-th best of the union is at least as good as either)
@@ -54,7 +57,7 @@ struct F4SmemTail {
     uint32_t lnslot[kFEpiGroups][kFQ][kTListK + 1];  // ~slot of each entry
     uint32_t liu[kFEpiGroups][kFQ][kTListK + 1];     // i | u << 16 of each entry
     uint32_t tmem_base;
-    unsigned long long full[kFStages], empty[kFStages], tmem_full[2], tmem_empty[2], pd_full[2], pd_empty[2];
+    unsigned long long full[kFStages], empty[kFStages], tmem_full[2], tmem_empty[2], pd_full[kFPdRing], pd_empty[kFPdRing];
 };
 static_assert(sizeof(uint32_t) * kFQ * (kTListK + 1) >= sizeof(uint32_t) * kTQueueCap, "the queues fit over lnslot[1]");
 constexpr size_t kF4SmemBytes = kFASmemBytes + kFStages * kFStageBytes + sizeof(F4SmemTail) + 128;
@@ -141,9 +144,11 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s.tmem_full[i], 1);
-            mbar_init(&s.tmem_empty[i], 4);  // the four warps of the group that owns the stage
+            mbar_init(&s.tmem_empty[i], kFEpiWarps);
+        }
+        for (int i = 0; i < kFPdRing; ++i) {
             mbar_init(&s.pd_full[i], kFProdWarps);
-            mbar_init(&s.pd_empty[i], 4);
+            mbar_init(&s.pd_empty[i], kFEpiWarps);
         }
         for (int i = 0; i < 4; ++i)
             s.queue_count[i] = 0;
@@ -225,14 +230,12 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
 #pragma unroll
             for (int c = 0; c < 8; ++c)
                 v[c] = vn[c];
-            const int a = (int)(t & 1);
-            mbar_wait(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));  // epilogue of tile t - 2 done with pd[a]
-            const uint32_t pdv = row < row_end ? pc : kTPadRow;
-            s.pd[a][pr] = pdv;
-            s.pdf[a][pr] = (float)pdv;
+            const int a4 = (int)(t % kFPdRing);
+            mbar_wait(&s.pd_empty[a4], (uint32_t)(((t / kFPdRing) & 1) ^ 1));  // epilogue of tile t - 4 done with it
+            s.pdf[a4][pr] = (float)(row < row_end ? pc : kTPadRow);
             __syncwarp();
             if (lane == 0)
-                mbar_arrive(&s.pd_full[a]);
+                mbar_arrive(&s.pd_full[a4]);
         }
     } else if (warp == kFMmaWarp) {
         // ================================================================ MMA issuer
@@ -265,22 +268,32 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
         }
     } else {
         // ================================================================ epilogue: thread = (group, one query of the tile)
-        const int grp = warp >> 2, wq = warp & 3;  // group = accumulator stage = tile parity; wq = TMEM lane quadrant
+        const int grp = warp >> 2, wq = warp & 3;  // group = column half of every tile; wq = TMEM lane quadrant
         const int ql = wq * 32 + lane;
         const uint32_t pqv = s.pq[ql];
         const bool smem_lists = p.k <= (uint32_t)kTListK;
         const bool share_bounds = smem_lists && p.bounds != nullptr;
-        const int groups = smem_lists ? kFEpiGroups : 1;  // k > kTListK: one list per query in global memory, group 0 alone
+        // k > kTListK: one list per query in GLOBAL memory -- group 0 takes both column halves, group 1 only keeps the
+        // barrier counts right
+        const bool both_halves = !smem_lists;
+        const int groups = smem_lists ? kFEpiGroups : 1;
         uint32_t (*queue)[kTQueueCap / 4] = reinterpret_cast<uint32_t (*)[kTQueueCap / 4]>(&s.lnslot[1][0][0]);
         const uint32_t kk = p.k;
         // this thread's own list: length, and its worst entry once it is full (counts, ~slot, position)
         uint32_t llen = 0, w_i = 0, w_u = 1, w_ns = 0, w_pos = 0;
-        for (uint64_t t = (uint64_t)grp; t < n_tiles && grp < groups; t += (uint64_t)groups) {
+        for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;
-            const int a = (int)(t & 1);  // (== grp when both groups work)
-            const uint32_t acc_ph = (uint32_t)((t >> 1) & 1);
-            mbar_wait(&s.pd_full[a], acc_ph);
-            mbar_wait(&s.tmem_full[a], acc_ph);
+            const int a = (int)(t & 1), a4 = (int)(t % kFPdRing);
+            if (both_halves && grp == 1) {  // nothing to do but to release what group 0 does not wait for
+                mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1));
+                if (lane == 0) {
+                    mbar_arrive(&s.tmem_empty[a]);
+                    mbar_arrive(&s.pd_empty[a4]);
+                }
+                continue;
+            }
+            mbar_wait(&s.pd_full[a4], (uint32_t)((t / kFPdRing) & 1));
+            mbar_wait(&s.tmem_full[a], (uint32_t)((t >> 1) & 1));
             tc_fence_after();
             // The filter bound of this tile: the tightest of (1) the worst entry of this thread's own full list -- strict:
             // its rows arrive from the highest slot down, so a row that merely ties loses; (2) the worst entry of the OTHER
@@ -310,13 +323,21 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                 if (have)
                     s.thr[grp][ql] = make_uint4(bu + bi, bi, bi * pqv, bw);
             }
-            // 32-column blocks from the HIGHEST rows down
-            for (int b = kFD / 32 - 1; b >= 0; --b) {
+            // This group's 112 columns in 32-column blocks from the HIGHEST rows down: columns base + 80, 48, 16, and the
+            // block at base + 0 of which only the lower 16 columns are new (the read is 32 wide; the rest is masked).
+            // (k > kTListK: group 0 walks both halves, the upper one first.)
+            const int n_blocks = both_halves ? 8 : 4;
+#pragma unroll 1
+            for (int bi = 0; bi < n_blocks; ++bi) {
+                const int base = both_halves ? (bi < 4 ? kFGroupCols : 0) : (grp == 0 ? kFGroupCols : 0);
+                const int bq = bi & 3;
+                const int c0 = base + (bq < 3 ? 80 - 32 * bq : 0);       // first column of the block in the tile
+                const uint32_t new_cols = bq < 3 ? 0xFFFFFFFFu : 0x0000FFFFu;  // hits bit 8 r + 7 - j <-> column 8 r + j
                 uint32_t acc[32];  // f32 bit patterns of the counts
-                const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * kFD + b * 32);
+                const uint32_t taddr = tmem_base + ((uint32_t)(wq * 32) << 16) + (uint32_t)(a * kFD + c0);
                 RB_TMEM_LD32(acc, taddr);
                 asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (b == 0) {  // the accumulator stage is free as soon as the last block is in registers
+                if (bi == n_blocks - 1) {  // the accumulator stage is free as soon as the last block is in registers
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0)
@@ -326,9 +347,9 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                 // an integer below 2^24, so the f32 arithmetic is exact and +0 (not -0) stands for "equal"
                 uint32_t hm[4] = {0, 0, 0, 0};
                 {
-                    const uint4 th = s.thr[grp][ql];
+                    const uint4 th = s.thr[smem_lists ? grp : 0][ql];
                     const float neg_a = -(float)th.x, bw = (float)(int)(th.z - th.w), y = (float)th.y;
-                    const float4* pd4 = reinterpret_cast<const float4*>(&s.pdf[a][b * 32]);
+                    const float4* pd4 = reinterpret_cast<const float4*>(&s.pdf[a4][c0]);
 #pragma unroll
                     for (int g = 0; g < 8; ++g) {
                         const float4 pv = pd4[g];
@@ -341,11 +362,12 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                         }
                     }
                 }
-                const uint32_t any_hit = pqv == kXInvalid ? 0u : (hm[0] | hm[1] | hm[2] | hm[3]);
+                const uint32_t all_hits = pqv == kXInvalid ? 0u : (((hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0]) & new_cols);
+                const uint32_t any_hit = all_hits;
                 if (smem_lists) {
                     if (any_hit) {
                         // bit 8 r + 7 - j of `hits` <-> column 8 r + j of the block (exact_topk_i8_kernel_t has the notes)
-                        uint32_t hits = (hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0];
+                        uint32_t hits = all_hits;
                         uint32_t* ls = &s.lnslot[grp][ql][0];
                         uint32_t* li = &s.liu[grp][ql][0];
                         bool changed = false;
@@ -355,8 +377,8 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                             hits &= ~(1u << bit);
                             const uint32_t col = (bit & 24u) | (7u - (bit & 7u));
                             const uint32_t iv = (uint32_t)__float2uint_rn(__uint_as_float(select32(acc, col)));
-                            const uint32_t dl = (uint32_t)(b * 32) + col;
-                            const uint32_t pdv = s.pd[a][dl];
+                            const uint32_t dl = (uint32_t)c0 + col;
+                            const uint32_t pdv = (uint32_t)s.pdf[a4][dl];
                             if (pdv >= kTPadRow)  // a padding row can pass a non-strict bound with i_t = 0
                                 continue;
                             const uint64_t row = row_begin + tile * kFD + dl;
@@ -410,7 +432,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                     }
                 } else if (__any_sync(RB_FULL_MASK, any_hit != 0)) {
                     // k > kTListK: lists in global memory, warp-local slow path (rounds of 8 columns, highest rows first)
-                    const uint32_t hits = pqv == kXInvalid ? 0u : ((hm[3] << 24) | (hm[2] << 16) | (hm[1] << 8) | hm[0]);
+                    const uint32_t hits = all_hits;
 #pragma unroll 1
                     for (int r = 3; r >= 0; --r) {
                         uint32_t hit = (hits >> (8 * r)) & 0xFFu;
@@ -421,7 +443,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                             hit &= ~(0x80u >> j);
                             const uint32_t iv = (uint32_t)__float2uint_rn(__uint_as_float(select32(acc, (uint32_t)(r * 8 + j))));
                             uint32_t at = atomicAdd(&s.queue_count[wq], 1u);
-                            queue[wq][at] = ((uint32_t)ql << 24) | ((uint32_t)(b * 32 + r * 8 + j) << 16) | iv;
+                            queue[wq][at] = ((uint32_t)ql << 24) | ((uint32_t)(c0 + r * 8 + j) << 16) | iv;
                         }
                         __syncwarp();
                         const uint32_t qn = s.queue_count[wq];
@@ -430,11 +452,12 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                             for (uint32_t jj = 0; jj < 32 && base + jj < qn; ++jj) {
                                 uint32_t ev = __shfl_sync(RB_FULL_MASK, e, (int)jj);
                                 uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
-                                if (s.pd[a][dl] >= kTPadRow)
+                                const uint32_t pdq = (uint32_t)s.pdf[a4][dl];
+                                if (pdq >= kTPadRow)
                                     continue;
                                 if (tri && row_begin + tile * kFD + dl >= (uint64_t)q0 + eq)
                                     continue;
-                                uint32_t u = s.pq[eq] + s.pd[a][dl] - i;
+                                uint32_t u = s.pq[eq] + pdq - i;
                                 uint32_t slot = (uint32_t)(p.slot_base + row_begin + tile * kFD + dl);
                                 uint64_t key = ((uint64_t)exact_distance_bits(i, u) << 32) | (uint32_t)~slot;
                                 const size_t off = (out_base + q0 + eq) * p.k;
@@ -457,7 +480,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                 }
             }
             if (lane == 0)
-                mbar_arrive(&s.pd_empty[a]);
+                mbar_arrive(&s.pd_empty[a4]);
         }
         if (smem_lists) {
             // publish: every thread sorts its own list (closest first), the two groups meet, group 0 merges the two
