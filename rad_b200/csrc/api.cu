@@ -532,11 +532,7 @@ std::string configure_exact_kernels() {
         return {};
     RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)sizeof(rb::ExactSmem)));
-    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)rb::kTensorSmemBytes));
-    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)rb::kTensorSmemBytes));
-    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel_t<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)rb::kTensorSmemBytes));
     RB_CUDA(cudaFuncSetAttribute(rb::exact_topk_f4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)rb::kF4SmemBytes));
@@ -839,7 +835,7 @@ std::string build_new_rows(rb_index* ix, uint64_t const* keys, size_t n, std::ve
                 if (!tile_debug && (forced_kernel == 0 || forced_kernel == 5))
                     rb::exact_topk_f4_kernel<<<grid, rb::kFThreads, rb::kF4SmemBytes, d.stream>>>(ep);
                 else
-                    rb::exact_topk_i8_kernel_t<0><<<grid, rb::kTThreads, rb::kTensorSmemBytes, d.stream>>>(ep);
+                    rb::exact_topk_i8_kernel<<<grid, rb::kTThreads, rb::kTensorSmemBytes, d.stream>>>(ep);
                 ++launches;
                 if (tile_debug) {
                     unsigned long long hh[32];
@@ -1140,16 +1136,8 @@ std::string add_common(rb_index* ix, uint64_t const* keys, uint8_t const* host_v
 // ================================================================================================ search
 namespace {
 
-#ifndef RB_I8_TS_DEFAULT
-#define RB_I8_TS_DEFAULT 0  // 1: the tensor-core kernel keeps the query operand in tensor memory (MODE 2)
-#endif
-#ifndef RB_I8_PAIR_DEFAULT
-#define RB_I8_PAIR_DEFAULT 0  // 1: CTA pairs (cta_group::2) whenever the tensor-core kernel runs on more than one tile
-#endif
 struct ExactPlan {
     bool tensor;  // tcgen05 int8 kernel (128-query tiles, 256-row stages) instead of the POPC kernel (64 x 64)
-    bool pair;    // ... in its CTA-pair form (exact_topk_i8_kernel_t<1>)
-    bool ts;      // ... with the query operand in tensor memory (exact_topk_i8_kernel_t<2>)
     bool f4;      // the FP4 tensor-core kernel (exact_topk_f4_kernel: kind::mxf4, 224-row tiles) -- the default tensor path
     uint32_t chunks;
     uint64_t chunk_rows;
@@ -1157,13 +1145,12 @@ struct ExactPlan {
     size_t bounds_off;            // u64[Q] shared k-th-distance bounds (tensor-core kernels), from the workspace start
 };
 
-// RB_EXACT_KERNEL=popc|f4|i8|i8x2|i8ts forces one of the bit-identical kernels (tests, profiling)
+// RB_EXACT_KERNEL=popc|f4|i8 forces one of the bit-identical kernels (tests, profiling)
 int exact_kernel_override() {
     char const* e = std::getenv("RB_EXACT_KERNEL");  // read per call: tests flip it between calls
     if (!e)
         return 0;
-    return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : std::strcmp(e, "i8x2") == 0 ? 3
-           : std::strcmp(e, "i8ts") == 0 ? 4 : std::strcmp(e, "f4") == 0 ? 5 : 0;
+    return std::strcmp(e, "popc") == 0 ? 1 : std::strcmp(e, "i8") == 0 ? 2 : std::strcmp(e, "f4") == 0 ? 5 : 0;
 }
 
 // SMs of the current device (148 on a B200; the same figure when no device is visible, so that workspace sizes can
@@ -1185,16 +1172,11 @@ ExactPlan plan_exact(uint64_t rows, uint64_t nq, uint32_t k) {
     // pairs per CTA to amortise unpacking the queries and warming up the per-CTA top-k lists (measured crossover
     // with the POPC kernel: about 1e9 pairs)
     p.tensor = forced >= 2 || (forced == 0 && nq >= 64 && rows * nq >= 2000000000ull);
-    // CTA pairs (cta_group::2): two adjacent query tiles share every unpacked database tile
-    p.pair = forced == 3 || (forced == 0 && p.tensor && RB_I8_PAIR_DEFAULT && nq > (uint64_t)rb::kTQ);
-    p.ts = forced == 4 || (forced == 0 && p.tensor && !p.pair && RB_I8_TS_DEFAULT);
-    p.f4 = forced == 5 || (forced == 0 && p.tensor && !p.pair && !p.ts);
+    p.f4 = forced == 5 || (forced == 0 && p.tensor);  // the FP4 kernel unless kind::i8 is asked for
     const uint64_t tq = p.tensor ? rb::kTQ : rb::kXQ, td = p.f4 ? rb::kFD : p.tensor ? rb::kTD : rb::kXD;
     const uint64_t sms = current_sm_count();
     const uint64_t resident = p.tensor ? sms : 2 * sms;  // resident CTAs: one (tensor kernel) or two (POPC kernel) per SM
     uint64_t qtiles = std::max<uint64_t>(1, (nq + tq - 1) / tq);
-    if (p.pair)
-        qtiles = (qtiles + 1) & ~(uint64_t)1;
     uint64_t row_tiles = std::max<uint64_t>(1, (rows + td - 1) / td);
     // Database chunks: 3 to 8 waves of CTAs, and among those the count that leaves the LAST wave fullest -- all CTAs of a
     // launch run equally long, so 632 CTAs on 148 SMs (4.27 waves) cost five full waves (measured: 15 % of the launch)
@@ -1270,30 +1252,12 @@ std::string launch_exact(uint4 const* db, uint64_t rows, uint64_t slot_base, uin
         RB_CUDA(cudaMemsetAsync(dbg_dev, 0, 32 * sizeof(unsigned long long), stream));
         ep.debug_cycles = dbg_dev;
     }
-    if (pl.tensor && pl.pair) {
-        unsigned qt = (unsigned)((nq + rb::kTQ - 1) / rb::kTQ);
-        qt = (qt + 1u) & ~1u;  // whole pairs: the odd CTA of the last pair has no valid query but unpacks its half
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3(qt, pl.chunks);
-        cfg.blockDim = dim3(rb::kTThreads);
-        cfg.dynamicSmemBytes = rb::kTensorSmemBytes;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 2;
-        attr[0].val.clusterDim.y = 1;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        RB_CUDA(cudaLaunchKernelEx(&cfg, rb::exact_topk_i8_kernel_t<1>, ep));
-    } else if (pl.tensor) {
+    if (pl.tensor) {
         dim3 grid((unsigned)((nq + rb::kTQ - 1) / rb::kTQ), pl.chunks);  // query tiles fastest: CTAs resident
         if (pl.f4)
             rb::exact_topk_f4_kernel<<<grid, rb::kFThreads, rb::kF4SmemBytes, stream>>>(ep);
-        else if (pl.ts)
-            rb::exact_topk_i8_kernel_t<2><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);
         else
-            rb::exact_topk_i8_kernel_t<0><<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
+            rb::exact_topk_i8_kernel<<<grid, rb::kTThreads, rb::kTensorSmemBytes, stream>>>(ep);  // together share rows
     } else {
         dim3 grid(pl.chunks, (unsigned)((nq + rb::kXQ - 1) / rb::kXQ));
         rb::exact_topk_kernel<<<grid, rb::kXThreads, sizeof(rb::ExactSmem), stream>>>(ep);

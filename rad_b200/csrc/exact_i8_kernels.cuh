@@ -63,62 +63,6 @@ static_assert(kTensorSmemBytes <= 232448, "227 KB of shared memory per CTA");
 
 // ---------------------------------------------------------------------------------------------- PTX helpers
 // (smem_u32, mbar_init, mbar_arrive, mbar_wait: device_common.cuh)
-// ---- cluster (CTA pair) variants: barriers and popcounts of the peer CTA are reached through shared::cluster addresses
-__device__ __forceinline__ uint32_t cluster_rank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ uint32_t map_to_cta(const void* local, uint32_t rank) {
-    uint32_t r;
-    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_u32(local)), "r"(rank));
-    return r;
-}
-__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
-}
-__device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, uint32_t v) {
-    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_cluster(void* bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2, %3;\n\t"
-            "selp.b32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)
-            : "memory");
-    } while (!done);
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tc_commit_pair(void* bar) {  // arrives on the barrier at this offset in BOTH CTAs
-    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(smem_u32(bar)), "h"((unsigned short)3)
-                 : "memory");
-}
-// D[tmem] (+)= A[tmem] * B[smem]
-__device__ __forceinline__ void tc_mma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
-                                             uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-__device__ __forceinline__ void tc_mma_i8_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                               uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -145,7 +89,6 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 // instruction descriptor (InstrDescriptor): c_format = S32 (2) at [4,6), a/b format = UINT8 (0), both K-major,
 // N >> 3 at [17,23), M >> 4 at [24,29)
 constexpr uint32_t kIdescI8 = (2u << 4) | ((uint32_t)(kTD >> 3) << 17) | ((uint32_t)(kTQ >> 4) << 24);
-constexpr uint32_t kIdescI8Pair = (2u << 4) | ((uint32_t)(kTD >> 3) << 17) | ((uint32_t)((2 * kTQ) >> 4) << 24);
 
 // 32 fingerprint bits -> 32 bytes as two 16-byte K pieces.  Any fixed bit -> K position mapping works as long as both
 // operands use it, so the cheapest one is taken: output word j holds bits j, j+8, j+16, j+24 of the input word.
@@ -207,42 +150,26 @@ constexpr uint32_t kTPadRow = 4096;
 
 // grid = (query tiles of 128, database chunks); ExactParams as for exact_topk_kernel with chunk_rows a multiple of kTD
 //
-// PAIR = true: the kernel is launched in clusters of two CTAs along x (two adjacent query tiles, the same database
-// chunk) and the MMAs are `cta_group::2` (M = 256: each CTA's own 128 queries; N = 256: each CTA unpacks and stores
-// HALF of every database tile, 128 rows, and the tensor cores of both SMs read both halves).  Per unit of MMA work a
-// CTA then unpacks half as many rows and its shared-memory port serves 8 KB instead of 12 KB per MMA; the 64 KB B
-// ring holds 4 stages of 128 fingerprint bits instead of 2.  Only the leader CTA (rank 0) issues MMAs; `full` and
-// `tmem_empty` live in the leader and collect arrivals from both CTAs, `tcgen05.commit` multicasts `empty` and
-// `tmem_full` to both, and the row popcounts are written into both CTAs' side arrays through shared::cluster stores.
-//
-// MODE 2 (TS): the query operand lives in TENSOR MEMORY (tcgen05.mma with A from TMEM: 137 instead of 166 cycles per
-// M128 N256 K32 instruction, and no operand bytes of A through the shared-memory port).  TMEM then holds A (columns
-// 256..511) and ONE 256-column accumulator, so the MMAs of a tile wait for the epilogue of the previous one; the
-// 128 KB of shared memory that A leaves make the B ring 6 stages deep.
-template <int MODE>
-__global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactParams p) {
-    constexpr bool PAIR = MODE == 1, TS = MODE == 2;
-    constexpr int STAGES = PAIR ? 4 : TS ? 6 : kTStages;    // B ring stages
-    constexpr int PIECES = PAIR ? 8 : kTPieces;             // K pieces per stage
+// (Round 1 also carried a CTA-pair form -- cta_group::2, half of every database tile unpacked per CTA -- and a form with
+// the query operand in tensor memory; both were bit-identical and no faster (DESIGN.md section 4 has the measurements)
+// and went when exact_topk_f4_kernel became the default tensor path.)
+__global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel(ExactParams p) {
+    constexpr int STAGES = kTStages;                        // B ring stages
+    constexpr int PIECES = kTPieces;                        // K pieces per stage
     constexpr int STEPS = 64 / PIECES;                      // stages per database tile
-    constexpr int BROWS = PAIR ? kTD / 2 : kTD;             // database rows this CTA unpacks per tile
     constexpr uint32_t SBO_B = PIECES * kLBO;
-    constexpr uint32_t STAGE_BYTES = (BROWS / 8) * SBO_B;
-    static_assert(TS ? STAGES * STAGE_BYTES == kASmemBytes + kTStages * kBStageBytes
-                     : STAGES * STAGE_BYTES == kTStages * kBStageBytes,
-                  "the B ring is 64 KB behind the query operand, or all 192 KB without it");
-    const uint32_t rank = PAIR ? cluster_rank() : 0u;
+    constexpr uint32_t STAGE_BYTES = (kTD / 8) * SBO_B;
     // no swizzle: the operand descriptors only need 16-byte alignment, which dynamic shared memory guarantees; the
     // array is used directly so that every access stays in the shared address space (LDS / STS, not generic LD / ST)
     extern __shared__ __align__(1024) unsigned char raw[];
     unsigned char* smem_a = raw;
-    unsigned char* smem_b = TS ? raw : raw + kASmemBytes;
+    unsigned char* smem_b = raw + kASmemBytes;
     TensorSmemTail& s = *reinterpret_cast<TensorSmemTail*>(raw + kASmemBytes + kTStages * kBStageBytes);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // Triangular form (the batch tile of the build, ExactParams::tri): blockIdx.y is a LEVEL, not a chunk; the level's
     // queries are the first tri_cnt[level] rows of the one array, query q sees rows [0, q), and the CTAs with the most
     // rows in front of them come first in launch order.
-    const bool tri = !PAIR && !TS && p.tri != 0;
+    const bool tri = p.tri != 0;
     const uint32_t qcount = tri ? p.tri_cnt[blockIdx.y] : p.query_count;
     const uint32_t q0 = (tri ? gridDim.x - 1 - blockIdx.x : blockIdx.x) * kTQ;  // may lie past the last query (the odd
                                                                                 // CTA of the last pair): all rows invalid
@@ -276,7 +203,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         s.pq[r] = q < qcount ? pc : kXInvalid;
         s.thr[r] = make_uint4(0, 1, 0, 2048);  // list not full: every valid row (|d| < 2048) passes, padding rows do not
     }
-    if (!TS) {
+    {
         const uint32_t* q32 = reinterpret_cast<const uint32_t*>(p.queries);
         for (int idx = tid; idx < kTQ * 64; idx += kTThreads) {
             int r = idx & (kTQ - 1), k16 = idx >> 7;
@@ -287,7 +214,7 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         }
     }
     if (tid == 0) {
-        constexpr uint32_t ctas = PAIR ? 2 : 1;
+        constexpr uint32_t ctas = 1;
         for (int i = 0; i < STAGES; ++i) {
             mbar_init(&s.full[i], ctas * kTProdWarps);  // one arrival per producer WARP (256 arrivals on one word serialise)
             mbar_init(&s.empty[i], 1);
@@ -303,57 +230,15 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == kTMmaWarp) {
-        if (PAIR) {
-            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&s.tmem_base))
-                         : "memory");
-            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-        } else {
-            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&s.tmem_base))
-                         : "memory");
-            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-        }
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&s.tmem_base))
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     fence_proxy_async();  // the A operand was written through the generic proxy
     tc_fence_before();
-    if (PAIR)
-        cluster_sync_all();  // both CTAs' barriers are initialised and both A operands are in place
-    else
-        __syncthreads();
+    __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = s.tmem_base;
-    if (TS) {
-        // the query tile goes to tensor memory: thread = query = TMEM lane, 4 columns per 16-byte K piece in the piece
-        // order of the database operand, written 32 columns (8 pieces = 128 fingerprint bits) at a time
-        if (warp < kTEpiWarps) {
-            const uint32_t q = q0 + (uint32_t)tid;
-            const uint4* qrow = p.queries + (size_t)q * 8;
-#pragma unroll 1
-            for (int c = 0; c < 8; ++c) {
-                const uint4 v = q < qcount ? __ldg(qrow + c) : make_uint4(0, 0, 0, 0);
-                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-                uint32_t r[32];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const uint4 u = unpack_half_query(w[j >> 1], j & 1);
-                    r[j * 4 + 0] = u.x, r[j * 4 + 1] = u.y, r[j * 4 + 2] = u.z, r[j * 4 + 3] = u.w;
-                }
-                const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)(256 + c * 32);
-                asm volatile(
-                    "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-                    "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-                    "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
-                    ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
-                      "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]),
-                      "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]),
-                      "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
-                    : "memory");
-            }
-            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-        }
-        tc_fence_before();
-        __syncthreads();
-        tc_fence_after();
-    }
     const bool dbg = p.debug_cycles != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
     unsigned long long dbg_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const long long dbg_start = clock64();
@@ -361,53 +246,6 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
     if (warp >= kTProdWarp0) {
         // ================================================================ producers: one database row per thread
         const int pr = tid - kTProdWarp0 * 32;  // 0 .. 255
-        if constexpr (PAIR) {
-            // two threads per row (row = pr / 2 of this CTA's 128; half = which 64 bits of every 128-bit K chunk), so
-            // that all 256 producer threads work on every stage
-            const int prow = pr >> 1, half = pr & 1;
-            unsigned char* my_b = smem_b + (prow >> 3) * SBO_B + (prow & 7) * 16 + half * 4 * kLBO;
-            const uint32_t full_leader = map_to_cta(&s.full[0], 0);
-            for (uint64_t t = 0; t < n_tiles; ++t) {
-                const uint64_t tile = n_tiles - 1 - t;  // highest rows first (see exact_kernels.cuh)
-                const uint64_t row = row_begin + tile * kTD + rank * BROWS + prow;
-                uint2 v[8];
-#pragma unroll
-                for (int c = 0; c < 8; ++c)
-                    v[c] = row < row_end ? __ldg(reinterpret_cast<const uint2*>(p.db + row * 8 + c) + half)
-                                         : make_uint2(0, 0);
-                uint32_t pc = 0;
-#pragma unroll
-                for (int c = 0; c < 8; ++c) {
-                    pc += __popc(v[c].x) + __popc(v[c].y);
-                    const uint64_t g = t * STEPS + c;
-                    const int st = (int)(g & (STAGES - 1));
-                    mbar_wait_cluster(&s.empty[st], (uint32_t)(((g / STAGES) & 1) ^ 1));
-                    unsigned char* dst = my_b + st * STAGE_BYTES;
-                    const uint32_t w[2] = {v[c].x, v[c].y};
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)  // K piece c * 8 + half * 4 + j  <->  A piece of the same index
-                        *reinterpret_cast<uint4*>(dst + j * kLBO) = unpack_half_db(w[j >> 1], j & 1);
-                    fence_proxy_async();
-                    __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive_cluster(full_leader + (uint32_t)st * 8u);
-                }
-                pc += __shfl_xor_sync(RB_FULL_MASK, pc, 1);
-                const int a = (int)(t & 1);
-                mbar_wait_cluster(&s.pd_empty[a], (uint32_t)(((t >> 1) & 1) ^ 1));  // both epilogues done with pd[a]
-                if (half == 0) {
-                    const uint32_t val = row < row_end ? pc : kTPadRow;
-                    st_cluster_u32(map_to_cta(&s.pd[a][rank * BROWS + prow], 0), val);
-                    st_cluster_u32(map_to_cta(&s.pd[a][rank * BROWS + prow], 1), val);
-                }
-                asm volatile("fence.acq_rel.cluster;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) {
-                    mbar_arrive_cluster(map_to_cta(&s.pd_full[a], 0));
-                    mbar_arrive_cluster(map_to_cta(&s.pd_full[a], 1));
-                }
-            }
-        } else {
         unsigned char* my_b = smem_b + (pr >> 3) * kSBO_B + (pr & 7) * 16;
         // the row of tile t + 1 is requested while tile t is unpacked (its L2 latency is off the hand-off path), and the
         // pieces of a stage are formed in registers BEFORE the wait for the stage, so that only stores follow the wait
@@ -463,26 +301,19 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
             if (lane == 0)
                 mbar_arrive(&s.pd_full[a]);
         }
-        }
     } else if (warp == kTMmaWarp) {
         // ================================================================ MMA issuer
         const uint64_t a_desc0 = make_smem_desc(smem_u32(smem_a), kLBO, kSBO_A);
         const uint64_t b_desc0 = make_smem_desc(smem_u32(smem_b), kLBO, SBO_B);
-        for (uint64_t t = 0; t < n_tiles && rank == 0; ++t) {  // in a pair only the leader CTA issues
-            const int a = TS ? 0 : (int)(t & 1);               // TS: one accumulator, one tile in flight
-            const uint32_t tph = TS ? (uint32_t)(t & 1) : (uint32_t)((t >> 1) & 1);
-            if (PAIR)
-                mbar_wait_cluster(&s.tmem_empty[a], tph ^ 1);
-            else
-                RB_TICK(1, mbar_wait(&s.tmem_empty[a], tph ^ 1));
+        for (uint64_t t = 0; t < n_tiles; ++t) {
+            const int a = (int)(t & 1);
+            const uint32_t tph = (uint32_t)((t >> 1) & 1);
+            RB_TICK(1, mbar_wait(&s.tmem_empty[a], tph ^ 1));
             tc_fence_after();
             for (int c = 0; c < STEPS; ++c) {
                 const uint64_t g = t * STEPS + c;
                 const int st = (int)(g % STAGES);
-                if (PAIR)
-                    mbar_wait_cluster(&s.full[st], (uint32_t)((g / STAGES) & 1));
-                else
-                    RB_TICK(2, mbar_wait(&s.full[st], (uint32_t)((g / STAGES) & 1)));
+                RB_TICK(2, mbar_wait(&s.full[st], (uint32_t)((g / STAGES) & 1)));
                 tc_fence_after();
                 if (lane == 0) {
 #pragma unroll
@@ -490,23 +321,11 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                         // K = 32 bytes per instruction = two 16-byte K pieces
                         uint64_t ad = a_desc0 + (uint64_t)(((c * PIECES + j * 2) * kLBO) >> 4);
                         uint64_t bd = b_desc0 + (uint64_t)((st * STAGE_BYTES + j * 2 * kLBO) >> 4);
-                        if (PAIR)
-                            tc_mma_i8_pair(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8Pair, (uint32_t)((c | j) != 0));
-                        else if (TS)
-                            tc_mma_i8_ts(tmem_base, tmem_base + (uint32_t)(256 + (c * PIECES + j * 2) * 4), bd, kIdescI8,
-                                         (uint32_t)((c | j) != 0));
-                        else
-                            tc_mma_i8(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8, (uint32_t)((c | j) != 0));
+                        tc_mma_i8(tmem_base + (uint32_t)a * kTD, ad, bd, kIdescI8, (uint32_t)((c | j) != 0));
                     }
-                    if (PAIR) {
-                        tc_commit_pair(&s.empty[st]);
-                        if (c == STEPS - 1)
-                            tc_commit_pair(&s.tmem_full[a]);
-                    } else {
-                        tc_commit(&s.empty[st]);
-                        if (c == STEPS - 1)
-                            tc_commit(&s.tmem_full[a]);
-                    }
+                    tc_commit(&s.empty[st]);
+                    if (c == STEPS - 1)
+                        tc_commit(&s.tmem_full[a]);
                 }
                 __syncwarp();
             }
@@ -525,15 +344,10 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         for (uint64_t t = 0; t < n_tiles; ++t) {
             const uint64_t tile = n_tiles - 1 - t;
             const int a = (int)(t & 1);            // popcount side array of this tile
-            const int acc_i = TS ? 0 : a;          // accumulator stage (TS: the only one)
-            const uint32_t acc_ph = TS ? (uint32_t)(t & 1) : (uint32_t)((t >> 1) & 1);
-            if (PAIR) {
-                mbar_wait_cluster(&s.pd_full[a], (uint32_t)((t >> 1) & 1));
-                mbar_wait_cluster(&s.tmem_full[acc_i], acc_ph);
-            } else {
-                RB_TICK(0, mbar_wait(&s.pd_full[a], (uint32_t)((t >> 1) & 1)));
-                RB_TICK(1, mbar_wait(&s.tmem_full[acc_i], acc_ph));
-            }
+            const int acc_i = a;                   // accumulator stage
+            const uint32_t acc_ph = (uint32_t)((t >> 1) & 1);
+            RB_TICK(0, mbar_wait(&s.pd_full[a], acc_ph));
+            RB_TICK(1, mbar_wait(&s.tmem_full[acc_i], acc_ph));
             tc_fence_after();
             // Shared bounds.  Every CTA starts with empty lists, and until a list is full and tight nearly every pair
             // survives the filter (about k ln(rows/k) survivors per query and CTA, ~1.5 k cycles each on the slow path:
@@ -566,12 +380,8 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                 if (b == 0) {  // the accumulator stage is free as soon as the last block is in registers
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) {
-                        if (PAIR)
-                            mbar_arrive_cluster(map_to_cta(&s.tmem_empty[a], 0));
-                        else
-                            mbar_arrive(&s.tmem_empty[acc_i]);
-                    }
+                    if (lane == 0)
+                        mbar_arrive(&s.tmem_empty[acc_i]);
                 }
                 // exact integer filter, 3 instructions per pair: the pair passes iff
                 //     i * A + w > B + y * |d|      (A = u_t + i_t, y = i_t, B = i_t |q|, w = 0; see exact_kernels.cuh)
@@ -740,14 +550,8 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
                     dbg_acc[7] += qn_total;
                 }
             }
-            if (lane == 0) {
-                if (PAIR) {
-                    mbar_arrive_cluster(map_to_cta(&s.pd_empty[a], 0));
-                    mbar_arrive_cluster(map_to_cta(&s.pd_empty[a], 1));
-                } else {
-                    mbar_arrive(&s.pd_empty[a]);
-                }
-            }
+            if (lane == 0)
+                mbar_arrive(&s.pd_empty[a]);
         }
         if (p.debug_cycles != nullptr && blockIdx.x == 0 && blockIdx.y == 0) {
             atomicAdd(p.debug_cycles + 29, n_hits);
@@ -787,16 +591,9 @@ __global__ void __launch_bounds__(kTThreads, 1) exact_topk_i8_kernel_t(ExactPara
         p.debug_cycles[31] = n_tiles;
     }
     tc_fence_before();
-    if (PAIR)
-        cluster_sync_all();  // no CTA may leave (or free its TMEM) while its peer still reads its shared memory
-    else
-        __syncthreads();
-    if (warp == kTMmaWarp) {
-        if (PAIR)
-            asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
-        else
-            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
-    }
+    __syncthreads();
+    if (warp == kTMmaWarp)
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
 }
 
 }  // namespace rb

@@ -14,11 +14,11 @@ from rad_b200.index import Index
 pytestmark = pytest.mark.gpu
 
 
-@pytest.fixture(autouse=True, params=["popc", "f4", "i8", "i8x2", "i8ts"])
+@pytest.fixture(autouse=True, params=["popc", "f4", "i8"])
 def exact_kernel(request, monkeypatch):
-    """Every test of this module runs against ALL exact-search kernels: the POPC-pipe kernel, the tcgen05 int8
-    tensor-core kernel, its CTA-pair (cta_group::2) form and its form with the query operand in tensor memory
-    (rad_b200/csrc/exact_i8_kernels.cuh); the library reads RB_EXACT_KERNEL on every call."""
+    """Every test of this module runs against ALL exact-search kernels: the POPC-pipe kernel, the FP4 tensor-core
+    kernel (tcgen05.mma kind::mxf4, rad_b200/csrc/exact_f4_kernels.cuh -- the default above 2e9 pairs) and the int8
+    tensor-core kernel (kind::i8, exact_i8_kernels.cuh); the library reads RB_EXACT_KERNEL on every call."""
     monkeypatch.setenv("RB_EXACT_KERNEL", request.param)
     return request.param
 
