@@ -24,9 +24,13 @@ namespace rb {
 
 constexpr int kFQ = 128;               // queries per CTA (UMMA M)
 constexpr int kFD = 224;               // database rows per tile (UMMA N)
-constexpr int kFPieces = 8;            // 16-byte K pieces (32 fingerprint bits each) per B stage
-constexpr int kFStages = 4;            // B ring: 4 stages = the 1024 bits of one tile
+#ifndef RB_F4_PIECES
+#define RB_F4_PIECES 16
+#endif
+constexpr int kFPieces = RB_F4_PIECES; // 16-byte K pieces (32 fingerprint bits each) per B stage: 16 (8: 2 % slower --
+                                       // one fence.proxy.async + hand-off per 4 MMAs instead of per 8)
 constexpr int kFSteps = 32 / kFPieces; // stages per database tile
+constexpr int kFStages = kFSteps;      // B ring = the 1024 bits of one tile: 2 stages of 512 bits
 // TWO epilogue groups of four warps (a warp reaches the TMEM lanes 32 (warp % 4) ..: warps 0-3 and 4-7 both cover all
 // 128 queries).  Both groups work on EVERY tile, group 0 on its columns 112..223, group 1 on 0..111, so an accumulator
 // stage is held for half an epilogue and the epilogues of consecutive tiles run back to back.  (Four warps took 6.6 k
@@ -207,21 +211,25 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
             }
             uint32_t pc = 0;
 #pragma unroll
-            for (int h = 0; h < kFSteps; ++h) {  // stage h of the tile = fingerprint words 8 h .. 8 h + 7 = uint4 2 h, 2 h + 1
-                pc += popc4(v[2 * h]) + popc4(v[2 * h + 1]);
-                const uint32_t w[8] = {v[2 * h].x, v[2 * h].y, v[2 * h].z, v[2 * h].w,
-                                       v[2 * h + 1].x, v[2 * h + 1].y, v[2 * h + 1].z, v[2 * h + 1].w};
+            for (int h = 0; h < kFSteps; ++h) {  // stage h of the tile = fingerprint words kFPieces h .. kFPieces (h + 1) - 1
                 const uint64_t g = t * kFSteps + h;
                 const int st = (int)(g % kFStages);
-                uint4 u[kFPieces];
-#pragma unroll
-                for (int j = 0; j < kFPieces; ++j)  // K piece 8 h + j  <->  A piece of the same index
-                    u[j] = unpack_f4_db(w[j]);
-                mbar_wait(&s.empty[st], (uint32_t)(((g / kFStages) & 1) ^ 1));
                 unsigned char* dst = my_b + st * kFStageBytes;
 #pragma unroll
-                for (int j = 0; j < kFPieces; ++j)
-                    *reinterpret_cast<uint4*>(dst + j * kLBO) = u[j];
+                for (int sub = 0; sub < kFPieces / 8; ++sub) {  // eight words (two uint4) at a time
+                    const int c4 = h * (kFPieces / 4) + 2 * sub;
+                    pc += popc4(v[c4]) + popc4(v[c4 + 1]);
+                    const uint32_t w[8] = {v[c4].x, v[c4].y, v[c4].z, v[c4].w, v[c4 + 1].x, v[c4 + 1].y, v[c4 + 1].z, v[c4 + 1].w};
+                    uint4 u[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)  // K piece kFPieces h + 8 sub + j  <->  A piece of the same index
+                        u[j] = unpack_f4_db(w[j]);
+                    if (sub == 0)
+                        mbar_wait(&s.empty[st], (uint32_t)(((g / kFStages) & 1) ^ 1));
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<uint4*>(dst + (sub * 8 + j) * kLBO) = u[j];
+                }
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0)
