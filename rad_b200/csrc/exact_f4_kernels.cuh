@@ -18,6 +18,8 @@
 // Results are bit-identical to exact_topk_kernel and exact_topk_i8_kernel_t (tests/test_gpu_exact.py runs every case
 // on all of them).
 #pragma once
+#include <cuda_fp16.h>
+
 #include "exact_i8_kernels.cuh"
 
 namespace rb {
@@ -49,7 +51,9 @@ constexpr int kFGroupCols = kFD / kFEpiGroups;           // 112 columns of a til
 
 struct F4SmemTail {
     uint32_t pq[kFQ];
-    float pdf[kFPdRing][kFD];  // row popcounts as f32 (kTPadRow for padding rows): the filter's operand; exact integers
+    __half pdf[kFPdRing][kFD];  // row popcounts as f16 (kTPadRow = 4096 for padding rows; integers <= 2048 and 4096 are
+                                // exact): the filter's operand -- eight per 16-byte broadcast read, the shared-memory
+                                // data pipe is what bounds this kernel
     uint4 thr[kFEpiGroups][kFQ];       // the filter thresholds of thread (group, query): written by that thread only
     uint32_t worst[kFEpiGroups][kFQ];  // i | u << 16 of the worst entry of that thread's FULL list, 0 before (read by
                                        // the other group: the k-th best of the union is at least as good as either)
@@ -240,7 +244,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                 v[c] = vn[c];
             const int a4 = (int)(t % kFPdRing);
             mbar_wait(&s.pd_empty[a4], (uint32_t)(((t / kFPdRing) & 1) ^ 1));  // epilogue of tile t - 4 done with it
-            s.pdf[a4][pr] = (float)(row < row_end ? pc : kTPadRow);
+            s.pdf[a4][pr] = __float2half_rn((float)(row < row_end ? pc : kTPadRow));
             __syncwarp();
             if (lane == 0)
                 mbar_arrive(&s.pd_full[a4]);
@@ -335,6 +339,8 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
             // block at base + 0 of which only the lower 16 columns are new (the read is 32 wide; the rest is masked).
             // (k > kTListK: group 0 walks both halves, the upper one first.)
             const int n_blocks = both_halves ? 8 : 4;
+            float neg_a = 0.f, bw = 0.f, y = 0.f;  // the filter's constants of this tile (see below)
+            bool reload_thr = true;
 #pragma unroll 1
             for (int bi = 0; bi < n_blocks; ++bi) {
                 const int base = both_halves ? (bi < 4 ? kFGroupCols : 0) : (grp == 0 ? kFGroupCols : 0);
@@ -355,18 +361,29 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                 // an integer below 2^24, so the f32 arithmetic is exact and +0 (not -0) stands for "equal"
                 uint32_t hm[4] = {0, 0, 0, 0};
                 {
-                    const uint4 th = s.thr[smem_lists ? grp : 0][ql];
-                    const float neg_a = -(float)th.x, bw = (float)(int)(th.z - th.w), y = (float)th.y;
-                    const float4* pd4 = reinterpret_cast<const float4*>(&s.pdf[a4][c0]);
+                    // (the thresholds change only at the start of a tile and when this thread's own list does -- or, for
+                    // k > kTListK, when another lane of the warp updates them: read them again only then)
+                    if (reload_thr || !smem_lists) {
+                        const uint4 th = s.thr[smem_lists ? grp : 0][ql];
+                        neg_a = -(float)th.x, bw = (float)(int)(th.z - th.w), y = (float)th.y;
+                        reload_thr = false;
+                    }
+                    const uint4* pd8 = reinterpret_cast<const uint4*>(&s.pdf[a4][c0]);  // eight f16 per read
 #pragma unroll
-                    for (int g = 0; g < 8; ++g) {
-                        const float4 pv = pd4[g];
-                        const float pdv[4] = {pv.x, pv.y, pv.z, pv.w};
+                    for (int g = 0; g < 4; ++g) {
+                        const uint4 pv = pd8[g];
+                        const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float r1 = __fmaf_rn(y, pdv[e], bw);
-                            const float dlt = __fmaf_rn(__uint_as_float(acc[g * 4 + e]), neg_a, r1);
-                            hm[g >> 1] = __funnelshift_l(__float_as_uint(dlt), hm[g >> 1], 1);
+                        for (int h2 = 0; h2 < 4; ++h2) {
+                            const float2 pf = __half22float2(*reinterpret_cast<const __half2*>(&pw[h2]));
+                            const float pdv[2] = {pf.x, pf.y};
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int col = g * 8 + h2 * 2 + e;
+                                const float r1 = __fmaf_rn(y, pdv[e], bw);
+                                const float dlt = __fmaf_rn(__uint_as_float(acc[col]), neg_a, r1);
+                                hm[col >> 3] = __funnelshift_l(__float_as_uint(dlt), hm[col >> 3], 1);
+                            }
                         }
                     }
                 }
@@ -386,7 +403,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                             const uint32_t col = (bit & 24u) | (7u - (bit & 7u));
                             const uint32_t iv = (uint32_t)__float2uint_rn(__uint_as_float(select32(acc, col)));
                             const uint32_t dl = (uint32_t)c0 + col;
-                            const uint32_t pdv = (uint32_t)s.pdf[a4][dl];
+                            const uint32_t pdv = (uint32_t)__half2float(s.pdf[a4][dl]);
                             if (pdv >= kTPadRow)  // a padding row can pass a non-strict bound with i_t = 0
                                 continue;
                             const uint64_t row = row_begin + tile * kFD + dl;
@@ -429,8 +446,10 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                         if (changed && llen == kk) {
                             // own list tighter: its worst entry becomes this thread's bound if it beats the one in use
                             const uint4 cur = s.thr[grp][ql];  // (x - y, y) = (u, i) of the bound in use; y = 1, x = 0 before any
-                            if (cur.x == 0 || w_i * (cur.x - cur.y) >= cur.y * w_u)
+                            if (cur.x == 0 || w_i * (cur.x - cur.y) >= cur.y * w_u) {
                                 s.thr[grp][ql] = make_uint4(w_u + w_i, w_i, w_i * pqv, 0);
+                                reload_thr = true;
+                            }
                             *reinterpret_cast<volatile uint32_t*>(&s.worst[grp][ql]) = w_i | (w_u << 16);
                             if (share_bounds && !tri)
                                 atomicMin(p.bounds + bound_base + q0 + ql,
@@ -460,7 +479,7 @@ __global__ void __launch_bounds__(kFThreads, 1) exact_topk_f4_kernel(ExactParams
                             for (uint32_t jj = 0; jj < 32 && base + jj < qn; ++jj) {
                                 uint32_t ev = __shfl_sync(RB_FULL_MASK, e, (int)jj);
                                 uint32_t eq = ev >> 24, dl = (ev >> 16) & 0xFFu, i = ev & 0xFFFFu;
-                                const uint32_t pdq = (uint32_t)s.pdf[a4][dl];
+                                const uint32_t pdq = (uint32_t)__half2float(s.pdf[a4][dl]);
                                 if (pdq >= kTPadRow)
                                     continue;
                                 if (tri && row_begin + tile * kFD + dl >= (uint64_t)q0 + eq)
