@@ -112,7 +112,8 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _serve(path, port):
+def _serve(path, port, workdir):
+    os.chdir(workdir)  # the server writes hnsw_top_nodes_cache_*.json into its working directory (rad/hnsw_server.py:171)
     sys.path.insert(0, REFERENCE)
     from rad.hnsw_server import run_hnsw_server  # noqa: PLC0415
     from rad_b200.index import Index  # noqa: PLC0415
@@ -120,7 +121,7 @@ def _serve(path, port):
                     debug=False)
 
 
-def test_http_server_and_remote_client(rad_modules, indexes, golden_dir):
+def test_http_server_and_remote_client(rad_modules, indexes, golden_dir, tmp_path):
     """rad/hnsw_server.py (FastAPI) serving rad_b200's Index in a forked child, rad's RemoteHNSWService as the client
     (the reference's tests/test_remote_hnsw.py:54-120 flow)."""
     pytest.importorskip("fastapi")
@@ -130,7 +131,7 @@ def test_http_server_and_remote_client(rad_modules, indexes, golden_dir):
     port = _free_port()
     path = os.path.join(golden_dir, "ref_n1000_m8.usearch")
     ctx = multiprocessing.get_context("fork")
-    proc = ctx.Process(target=_serve, args=(path, port), daemon=True)
+    proc = ctx.Process(target=_serve, args=(path, port, str(tmp_path)), daemon=True)
     proc.start()
     try:
         client = None
