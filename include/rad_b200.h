@@ -184,6 +184,20 @@ RB_EXPORT void rb_dedup_device(void const* d_vectors, uint64_t rows, void* d_rep
                                size_t workspace_bytes, uintptr_t stream, rb_error_t* error);
 RB_EXPORT void rb_popcounts_device(void const* d_vectors, uint64_t rows, void* d_popcounts, uintptr_t stream,
                                    rb_error_t* error);
+/* Index.join: one-to-one ("stable marriage") matching of two fingerprint sets -- usearch/include/usearch/index.hpp:
+ * 4330-4515 (the algorithm), usearch/python/lib.cpp:876-894 (the binding), usearch/python/usearch/index.py:1182-1212.
+ * The candidates of every "man" (row of the SMALLER set) among the "women" come from rb_search_device on the women's
+ * index (k = proposals; exact or ef-bounded): d_candidate_slots u32 [men x proposals] nearest first,
+ * d_candidate_distances f32 [men x proposals], d_candidate_counts i32 [men].  The matching is the one the reference's
+ * loop produces on ONE thread (ring of free men processed front to back; a woman leaves her husband only for a
+ * strictly nearer man), computed generation by generation on the device.  d_man_to_woman u32 [men] and
+ * d_woman_to_man u32 [women] receive slots, 0xFFFFFFFF = unmatched.  Synchronises `stream` once per generation. */
+RB_EXPORT size_t rb_stable_match_workspace_bytes(uint64_t men, uint64_t women);
+RB_EXPORT void rb_stable_match_device(void const* d_candidate_slots, void const* d_candidate_distances,
+                                      void const* d_candidate_counts, uint64_t men, uint64_t women, uint32_t proposals,
+                                      void* d_man_to_woman, void* d_woman_to_man, void* d_workspace,
+                                      size_t workspace_bytes, uintptr_t stream, uint64_t* generations_out,
+                                      uint64_t* engagements_out, rb_error_t* error);
 
 /* ---------------------------------------------------------------- one graph from G row shards (SURVEY.md section 8e row 3;
  * usearch has no counterpart: its multi-index `Indexes`, python/lib.cpp:417-498, only searches shards side by side).

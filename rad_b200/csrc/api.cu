@@ -19,6 +19,7 @@
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
 #include <cuda_runtime.h>
 
 #include "../../include/rad_b200.h"
@@ -2008,6 +2009,124 @@ void rb_dedup_device(void const* d_vectors, uint64_t rows, void* d_representativ
     }
     if (e != cudaSuccess)
         RB_FAIL(std::string("CUDA error in dedup: ") + cudaGetErrorString(e));
+}
+
+// ---------------------------------------------------------------------------------------------- join: stable matching
+namespace {
+struct JoinLayout {
+    size_t made, husband_dist, ring[2], next, keys[2], values[2], counters, tmp, tmp_bytes, total;
+};
+JoinLayout join_layout(uint64_t men, uint64_t women) {
+    JoinLayout L{};
+    auto take = [&](size_t bytes) {
+        size_t at = L.total;
+        L.total += (bytes + 255) & ~(size_t)255;
+        return at;
+    };
+    L.made = take(men * 4), L.husband_dist = take(women * 4);
+    L.ring[0] = take(men * 4), L.ring[1] = take(men * 4), L.next = take(men * 4);
+    L.keys[0] = take(men * 8), L.keys[1] = take(men * 8);
+    L.values[0] = take(men * 4), L.values[1] = take(men * 4);
+    L.counters = take(16);
+    size_t sort_tmp = 0, select_tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_tmp, (uint64_t*)nullptr, (uint64_t*)nullptr, (uint32_t*)nullptr,
+                                    (uint32_t*)nullptr, (int64_t)men);
+    cub::DeviceSelect::If(nullptr, select_tmp, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (int64_t)men,
+                          rb::JoinIsMan());
+    L.tmp_bytes = std::max(sort_tmp, select_tmp);
+    L.tmp = take(L.tmp_bytes);
+    return L;
+}
+}  // namespace
+
+size_t rb_stable_match_workspace_bytes(uint64_t men, uint64_t women) { return men ? join_layout(men, women).total : 0; }
+
+namespace {
+std::string stable_match(void const* d_candidate_slots, void const* d_candidate_distances,
+                         void const* d_candidate_counts, uint64_t men, uint64_t women, uint32_t proposals,
+                         void* d_man_to_woman, void* d_woman_to_man, void* d_workspace, size_t workspace_bytes,
+                         cudaStream_t stream, uint64_t* generations_out, uint64_t* engagements_out) {
+    if (men >= (1ull << 32) - 1 || women >= (1ull << 32) - 1)
+        return "rb_stable_match_device addresses at most 2^32 - 2 rows on either side";
+    if (men)
+        RB_CUDA(cudaMemsetAsync(d_man_to_woman, 0xFF, men * 4, stream));
+    if (women)
+        RB_CUDA(cudaMemsetAsync(d_woman_to_man, 0xFF, women * 4, stream));
+    if (!men || !women || !proposals)
+        return {};
+    const JoinLayout L = join_layout(men, women);
+    if (workspace_bytes < L.total)
+        return "workspace smaller than rb_stable_match_workspace_bytes(men, women)";
+    uint8_t* ws = static_cast<uint8_t*>(d_workspace);
+    uint32_t* ring[2] = {reinterpret_cast<uint32_t*>(ws + L.ring[0]), reinterpret_cast<uint32_t*>(ws + L.ring[1])};
+    uint64_t* keys[2] = {reinterpret_cast<uint64_t*>(ws + L.keys[0]), reinterpret_cast<uint64_t*>(ws + L.keys[1])};
+    uint32_t* values[2] = {reinterpret_cast<uint32_t*>(ws + L.values[0]), reinterpret_cast<uint32_t*>(ws + L.values[1])};
+    uint32_t* selected = reinterpret_cast<uint32_t*>(ws + L.counters);
+    rb::JoinParams p{};
+    p.cand_slots = static_cast<const uint32_t*>(d_candidate_slots);
+    p.cand_dist = static_cast<const uint32_t*>(d_candidate_distances);
+    p.cand_counts = static_cast<const int32_t*>(d_candidate_counts);
+    p.proposals = proposals;
+    p.made = reinterpret_cast<uint32_t*>(ws + L.made);
+    p.man_to_woman = static_cast<uint32_t*>(d_man_to_woman);
+    p.woman_to_man = static_cast<uint32_t*>(d_woman_to_man);
+    p.husband_dist = reinterpret_cast<uint32_t*>(ws + L.husband_dist);
+    p.next = reinterpret_cast<uint32_t*>(ws + L.next);
+    p.engagements = reinterpret_cast<unsigned long long*>(ws + L.counters + 8);
+    RB_CUDA(cudaMemsetAsync(p.made, 0, men * 4, stream));
+    RB_CUDA(cudaMemsetAsync(ws + L.counters, 0, 16, stream));
+    rb::join_init_kernel<<<(unsigned)((men + 255) / 256), 256, 0, stream>>>(ring[0], (uint32_t)men);
+    uint32_t length = (uint32_t)men;
+    uint64_t generations = 0;
+    for (int cur = 0; length; cur ^= 1, ++generations) {
+        p.ring = ring[cur];
+        p.length = length;
+        p.keys = keys[0], p.values = values[0];
+        const unsigned grid = (length + 255) / 256;
+        rb::join_propose_kernel<<<grid, 256, 0, stream>>>(p);
+        size_t tmp = L.tmp_bytes;
+        cudaError_t e = cub::DeviceRadixSort::SortPairs(ws + L.tmp, tmp, keys[0], keys[1], values[0], values[1],
+                                                        (int64_t)length, 0, 64, stream);
+        if (e == cudaSuccess) {
+            p.keys = keys[1], p.values = values[1];
+            rb::join_settle_kernel<<<grid, 256, 0, stream>>>(p);
+            tmp = L.tmp_bytes;
+            e = cub::DeviceSelect::If(ws + L.tmp, tmp, p.next, ring[cur ^ 1], selected, (int64_t)length, rb::JoinIsMan(),
+                                      stream);
+        }
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(&length, selected, 4, cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess)
+            return std::string("CUDA error in the matching: ") + cudaGetErrorString(e);
+    }
+    unsigned long long engaged = 0;
+    RB_CUDA(cudaMemcpyAsync(&engaged, p.engagements, 8, cudaMemcpyDeviceToHost, stream));
+    RB_CUDA(cudaStreamSynchronize(stream));
+    if (generations_out)
+        *generations_out = generations;
+    if (engagements_out)
+        *engagements_out = engaged;
+    return {};
+}
+}  // namespace
+
+void rb_stable_match_device(void const* d_candidate_slots, void const* d_candidate_distances,
+                            void const* d_candidate_counts, uint64_t men, uint64_t women, uint32_t proposals,
+                            void* d_man_to_woman, void* d_woman_to_man, void* d_workspace, size_t workspace_bytes,
+                            uintptr_t stream, uint64_t* generations_out, uint64_t* engagements_out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (generations_out)
+        *generations_out = 0;
+    if (engagements_out)
+        *engagements_out = 0;
+    std::string msg = stable_match(d_candidate_slots, d_candidate_distances, d_candidate_counts, men, women, proposals,
+                                   d_man_to_woman, d_woman_to_man, d_workspace, workspace_bytes,
+                                   reinterpret_cast<cudaStream_t>(stream), generations_out, engagements_out);
+    if (!msg.empty())
+        RB_FAIL(msg);
 }
 
 void rb_popcounts_device(void const* d_vectors, uint64_t rows, void* d_popcounts, uintptr_t stream_, rb_error_t* error) {

@@ -87,4 +87,107 @@ __global__ void __launch_bounds__(256) representative_kernel(const uint4* __rest
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Index.join: one-to-one matching of two fingerprint sets (usearch/include/usearch/index.hpp:4330-4515).  The reference
+// keeps a ring of free "men"; a popped man proposes to his next-nearest "woman" (the k-th answer of a search), a free
+// woman accepts, an engaged one leaves her husband only for a STRICTLY nearer man, and whoever loses goes to the back
+// of the ring.  With one thread the ring is processed in GENERATIONS: everybody appended while generation g is being
+// processed forms generation g + 1, in the order of the proposals that sent them there.  Women are independent inside
+// a generation, so a generation is three data-parallel steps here, and the matching is the one the reference's loop
+// produces on one thread (tests/model/join_model.py states that loop):
+//   join_propose_kernel   position i of the generation -> sort key (woman << 32 | i), value = distance bits
+//   cub radix sort        proposals grouped by woman, in ring order inside a group (library code)
+//   join_settle_kernel    one thread per woman walks her proposals in ring order; the loser of proposal i (the
+//                         proposer or the husband he replaces) is written to next[i]
+//   cub select            next[] without its holes = the next generation, in ring order (library code)
+constexpr uint32_t kJoinNone = 0xFFFFFFFFu;
+
+struct JoinParams {
+    const uint32_t* cand_slots;  // [men x proposals] women, nearest first (rb_search_device)
+    const uint32_t* cand_dist;   // [men x proposals] f32 bits
+    const int32_t* cand_counts;  // [men] valid candidates
+    uint32_t proposals;
+    uint32_t* made;              // [men] proposals made so far
+    uint32_t* man_to_woman;      // [men]
+    uint32_t* woman_to_man;      // [women]
+    uint32_t* husband_dist;      // [women] f32 bits
+    const uint32_t* ring;        // this generation, [length]
+    uint32_t length;
+    uint64_t* keys;              // [length]
+    uint32_t* values;            // [length]
+    uint32_t* next;              // [length]
+    unsigned long long* engagements;
+};
+
+__global__ void __launch_bounds__(256) join_propose_kernel(JoinParams p) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.length)
+        return;
+    const uint32_t man = p.ring[i];
+    const uint32_t c = p.made[man];
+    uint64_t key = ~0ull;
+    uint32_t value = 0, next = kJoinNone;
+    if (c < p.proposals) {  // a man who has used up his proposals leaves the ring (index.hpp:4440-4442)
+        p.made[man] = c + 1;
+        if ((int32_t)c < p.cand_counts[man]) {
+            key = (uint64_t)p.cand_slots[(size_t)man * p.proposals + c] << 32 | i;
+            value = p.cand_dist[(size_t)man * p.proposals + c];
+        } else {
+            // fewer answers than proposals: the reference asks the last woman again (candidates.back()), whose husband
+            // is by now at least as near as this man -- he is sent to the back of the ring
+            next = man;
+        }
+    }
+    p.keys[i] = key;
+    p.values[i] = value;
+    p.next[i] = next;
+}
+
+// keys / values: sorted.  The thread at the first proposal of a woman settles all of them.
+__global__ void __launch_bounds__(256) join_settle_kernel(JoinParams p) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.length)
+        return;
+    const uint64_t first = p.keys[t];
+    if (first == ~0ull)
+        return;
+    const uint32_t woman = (uint32_t)(first >> 32);
+    if (t && (uint32_t)(p.keys[t - 1] >> 32) == woman)
+        return;
+    uint32_t holder = p.woman_to_man[woman], holder_dist = p.husband_dist[woman];
+    unsigned long long engaged = 0;
+    for (uint32_t u = t; u < p.length; ++u) {
+        const uint64_t key = p.keys[u];
+        if ((uint32_t)(key >> 32) != woman)
+            break;
+        const uint32_t i = (uint32_t)key, man = p.ring[i], dist = p.values[u];
+        // non-negative floats order like their bits; strict: a tie keeps the husband (index.hpp:4467)
+        if (holder == kJoinNone || holder_dist > dist) {
+            if (holder != kJoinNone) {
+                p.man_to_woman[holder] = kJoinNone;
+                p.next[i] = holder;
+            }
+            holder = man, holder_dist = dist;
+            ++engaged;
+        } else {
+            p.next[i] = man;
+        }
+    }
+    p.woman_to_man[woman] = holder;
+    p.husband_dist[woman] = holder_dist;
+    p.man_to_woman[holder] = woman;
+    if (engaged)
+        atomicAdd(p.engagements, engaged);
+}
+
+__global__ void __launch_bounds__(256) join_init_kernel(uint32_t* ring, uint32_t men) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < men)
+        ring[i] = i;
+}
+
+struct JoinIsMan {
+    __host__ __device__ bool operator()(uint32_t v) const { return v != kJoinNone; }
+};
+
 }  // namespace rb

@@ -21,7 +21,7 @@ import os
 from collections.abc import Sequence
 from dataclasses import dataclass
 from inspect import signature
-from typing import Callable, Iterable, List, Optional, Union
+from typing import Callable, Dict, Iterable, List, Optional, Union
 
 import numpy as np
 
@@ -447,8 +447,14 @@ class Index:
     def copy(self):
         raise NotImplementedError("copy() is outside RAD's path and not implemented by rad_b200")
 
-    def join(self, *a, **k):
-        raise NotImplementedError("join() is outside RAD's path and not implemented by rad_b200")
+    def join(self, other: "Index", max_proposals: int = 0, exact: bool = False,
+             progress: Optional[ProgressCallback] = None) -> Dict[int, int]:
+        """One-to-one matching between the rows of ``self`` and ``other``: mapping from keys of ``self`` to keys of
+        ``other`` with no key used twice (reference: index.py:1182-1212, lib.cpp:876-894, index.hpp:4330-4515).  The
+        candidate searches and the proposals run on the GPU (``rad_b200/join.py``)."""
+        assert not progress or _match_signature(progress, [int, int], bool), "Invalid callback signature"
+        from .join import join as _join
+        return _join(self, other, max_proposals=max_proposals, exact=exact, progress=progress)
 
     def cluster(self, *a, **k):
         raise NotImplementedError("cluster() is outside RAD's path and not implemented by rad_b200")
