@@ -130,6 +130,13 @@ RB_EXPORT void rb_search(rb_index_t* index, uint8_t const* queries, size_t query
 RB_EXPORT void rb_search_device(rb_index_t* index, void const* d_queries, size_t query_count, size_t k, int exact,
                                 void* d_slots_out, void* d_distances_out, void* d_counts_out, rb_error_t* error);
 
+/* `cluster(query, level)` of usearch/include/usearch/index.hpp:3046-3079 for a batch: the greedy descent from the entry
+ * point down to and including `level` (level 0 stops at level 1, like the reference) -> the node where it ends
+ * (slots_out u32 [Q]) and its distance (distances_out f32 [Q]); device pointers, queries padded to 128 bytes.  The
+ * building block of Index.cluster (usearch/include/usearch/index_dense.hpp:1919-2080; rad_b200/cluster.py). */
+RB_EXPORT void rb_cluster_device(rb_index_t* index, void const* d_queries, size_t query_count, int level,
+                                 void* d_slots_out, void* d_distances_out, rb_error_t* error);
+
 /* ---------------------------------------------------------------- stateless device kernels (multi-GPU plumbing, bench)
  * Exact Tanimoto top-k of Q queries against a shard of `rows` fingerprints resident in HBM.
  * d_keys_out: u64 [Q x k], key = f32 distance bits << 32 | ~(slot_base + row) so that ascending key order IS the

@@ -1847,6 +1847,53 @@ void rb_search_device(rb_index_t* ix, void const* d_queries, size_t nq, size_t k
         RB_FAIL(err);
 }
 
+void rb_cluster_device(rb_index_t* ix, void const* d_queries, size_t nq, int level, void* d_slots_out,
+                       void* d_distances_out, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!nq)
+        return;
+    if (!ix->host.size())
+        RB_FAIL("No clusters to identify");  // index.hpp:3056-3057
+    std::string err = prepare_search(ix, 1);
+    if (!err.empty())
+        RB_FAIL(err);
+    if (level < 0 || level > ix->host.max_level)
+        RB_FAIL("level outside 0..max_level");
+    err = [&]() -> std::string {
+        DeviceState& d = ix->dev;
+        RB_CUDA(cudaMemsetAsync(d.counters, 0, 4 * sizeof(unsigned long long), d.stream));
+        RB_CUDA(cudaEventRecord(d.ev_begin, d.stream));
+        rb::ClusterParams cp;
+        cp.g = graph_view(ix);
+        cp.queries = static_cast<uint4 const*>(d_queries);
+        cp.query_count = (uint32_t)nq;
+        cp.entry = (uint32_t)ix->host.entry;
+        cp.max_level = ix->host.max_level;
+        cp.level = level;
+        cp.slots_out = static_cast<uint32_t*>(d_slots_out);
+        cp.dists_out = static_cast<float*>(d_distances_out);
+        cp.counters = d.counters;
+        unsigned blocks = (unsigned)std::min<size_t>((nq + 7) / 8, (size_t)d.sm_count * 8);
+        rb::cluster_kernel<<<blocks, 256, 0, d.stream>>>(cp);
+        RB_CUDA(cudaGetLastError());
+        RB_CUDA(cudaEventRecord(d.ev_end, d.stream));
+        RB_CUDA(cudaStreamSynchronize(d.stream));
+        float ms = 0;
+        RB_CUDA(cudaEventElapsedTime(&ms, d.ev_begin, d.ev_end));
+        unsigned long long counters[4];
+        RB_CUDA(cudaMemcpy(counters, d.counters, sizeof(counters), cudaMemcpyDeviceToHost));
+        ix->last.computed_distances = counters[0];
+        ix->last.visited_members = counters[1];
+        ix->last.batches = 0;
+        ix->last.kernel_launches = 1;
+        ix->last.device_ms = ms;
+        return {};
+    }();
+    if (!err.empty())
+        RB_FAIL(err);
+}
+
 size_t rb_exact_topk_workspace_bytes(uint64_t rows, uint64_t query_count, uint32_t k) {
     ExactPlan pl = plan_exact(rows, query_count, k);
     return pl.keys_bytes + pl.iu_bytes;

@@ -1301,4 +1301,41 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB) search_kernel(Searc
     }
 }
 
+// ------------------------------------------------------------------------------------------------ cluster_kernel
+// index.hpp:3046-3079 (`cluster(query, level)`): the greedy descent alone, from the entry point down to and including
+// `level` (never below level 1: neighbors_non_base_), and the reference-exact distance of where it ends.  One warp per
+// query, no shared memory.  Deterministic given the graph: on a graph the reference built it is the reference's answer.
+struct ClusterParams {
+    GraphView g;
+    const uint4* queries;
+    uint32_t query_count, entry;
+    int max_level, level;
+    uint32_t* slots_out;  // Q
+    float* dists_out;     // Q
+    unsigned long long* counters;
+};
+
+__global__ void __launch_bounds__(256) cluster_kernel(ClusterParams p) {
+    const int lane = threadIdx.x & 31, sub = lane & 7;
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    TraversalCounters tc{0, 0};
+    for (uint32_t qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; qi < p.query_count; qi += warps) {
+        const uint4 q4 = __ldg(p.queries + (size_t)qi * 8 + sub);
+        uint32_t cur = p.entry;
+        uint32_t cur_bits = warp_eval_one(p.g.fp, q4, cur);
+        tc.distances += 1;
+        warp_greedy_descent(p.g, q4, cur, cur_bits, p.max_level, (p.level <= 0 ? 1 : p.level) - 1, tc);
+        const uint32_t v = group8_inter_union(load_slice(p.g.fp, cur, sub), q4);
+        tc.distances += 1;  // the reference measures the member once more (index.hpp:3071)
+        if (lane == 0) {
+            p.slots_out[qi] = cur;
+            p.dists_out[qi] = __uint_as_float(exact_distance_bits(v & 0xFFFFu, v >> 16));
+        }
+    }
+    if (lane == 0) {
+        atomicAdd(p.counters + 0, (unsigned long long)tc.distances);
+        atomicAdd(p.counters + 1, (unsigned long long)tc.expansions);
+    }
+}
+
 }  // namespace rb

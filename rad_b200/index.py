@@ -165,6 +165,30 @@ class BatchMatches(Sequence):
         return f"usearch.BatchMatches({np.sum(self.counts)} across {len(self)} queries)"
 
 
+class Clustering:
+    """What ``Index.cluster`` returns (reference: index.py:384-409): the centroid of every query."""
+
+    def __init__(self, index: "Index", matches: BatchMatches, queries: Optional[np.ndarray] = None) -> None:
+        if queries is None:
+            queries = index.keys
+        self.index = index
+        self.queries = queries
+        self.matches = matches
+
+    def __repr__(self) -> str:
+        return f"usearch.Clustering(for {len(self.queries)} queries)"
+
+    @property
+    def centroids_popularity(self):
+        return np.unique(self.matches.keys, return_counts=True)
+
+    def members_of(self, centroid) -> np.ndarray:
+        return self.queries[self.matches.keys.flatten() == centroid]
+
+    def subcluster(self, centroid, **clustering_kwards) -> "Clustering":
+        return self.index.cluster(keys=self.members_of(centroid), **clustering_kwards)
+
+
 @dataclass
 class IndexStats:
     """Per-level statistics (usearch/python/lib.cpp:1007-1013)."""
@@ -456,8 +480,37 @@ class Index:
         from .join import join as _join
         return _join(self, other, max_proposals=max_proposals, exact=exact, progress=progress)
 
-    def cluster(self, *a, **k):
-        raise NotImplementedError("cluster() is outside RAD's path and not implemented by rad_b200")
+    def cluster(self, *, vectors: Optional[np.ndarray] = None, keys: Optional[np.ndarray] = None,
+                min_count: Optional[int] = None, max_count: Optional[int] = None, threads: int = 0,
+                log: Union[str, bool] = False, progress: Optional[ProgressCallback] = None) -> "Clustering":
+        """Clusters already indexed or provided ``vectors``, mapping them to centroids taken from an upper level of the
+        graph (reference: index.py:1214-1273, lib.cpp:758-875, index_dense.hpp:1919-2080; ``rad_b200/cluster.py``)."""
+        assert not progress or _match_signature(progress, [int, int], bool), "Invalid callback signature"
+        from .cluster import cluster as _cluster
+        if vectors is not None:
+            assert keys is None, "You can either cluster vectors or member keys"
+            if vectors.ndim != 2:
+                raise ValueError("Expects a matrix of queries to add!")
+            if vectors.shape[1] != self.ndim // 8:
+                raise ValueError("The number of vector dimensions doesn't match!")
+            queries, members = np.ascontiguousarray(vectors, dtype=np.uint8), None
+        else:
+            members = np.asarray(self.keys if keys is None else keys).astype(Key)
+            slots = np.atleast_1d(self.get_node_ids_from_keys(members))
+            if (slots < 0).any():
+                raise RuntimeError("Key missing!")                            # index_dense.hpp:865-866
+            queries = np.empty((len(members), self.ndim // 8), dtype=np.uint8)
+            err = C.c_char_p()
+            sl = np.ascontiguousarray(slots, dtype=np.uint64)
+            self._lib.rb_get_vectors(self._handle(), sl.ctypes.data, len(sl), queries.ctypes.data, C.byref(err))
+            self._check(err)
+        ckeys, dists, visited, computed, _ = _cluster(self, queries, int(min_count or 0), int(max_count or 0))
+        n = len(queries)
+        if progress:
+            progress(n, n)
+        matches = BatchMatches(ckeys.reshape(n, 1).astype(Key), dists.reshape(n, 1), np.ones(n, dtype=np.int64),
+                               visited, computed)
+        return Clustering(self, matches, members)
 
     def clear(self):
         """Erases all vectors from the index, preserving the allocated space (reference: index.py:1150-1152)."""
