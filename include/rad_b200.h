@@ -163,6 +163,17 @@ RB_EXPORT void rb_exact_topk_device_noalloc(void const* d_database, uint64_t row
                                             uintptr_t stream, rb_error_t* error);
 RB_EXPORT void rb_merge_topk_device(void const* d_partial_keys, uint32_t parts, uint64_t query_count, uint32_t k,
                                     void* d_keys_out, uintptr_t stream, rb_error_t* error);
+/* Multi-GPU search behind the C ABI (the reference's `Indexes`, usearch/python/lib.cpp:417-498, searches its shards side
+ * by side and merges by index.hpp:2625-2645).  Every rank calls this with its shard `index` (rows in global slots
+ * slot_base ..), the SAME queries (device, 128 bytes each) and its NCCL communicator (an `ncclComm_t` passed as an
+ * integer): local search (exact or ef-bounded) -> keys in global slots -> ncclAllGather on the handle's stream ->
+ * k-way merge.  d_keys_out: u64 [Q x k] on every rank, the format of rb_exact_topk_device (rb_unpack_topk_device
+ * splits it).  NCCL is loaded with dlopen at the first call (the copy already in the process, else libnccl.so.2):
+ * the library does not link against it.  An empty shard takes part with no candidates. */
+RB_EXPORT size_t rb_sharded_search_workspace_bytes(size_t query_count, size_t k, uint32_t world);
+RB_EXPORT void rb_sharded_search_device(rb_index_t* index, uint64_t slot_base, void const* d_queries,
+                                        size_t query_count, size_t k, int exact, uintptr_t nccl_comm, void* d_keys_out,
+                                        void* d_workspace, size_t workspace_bytes, rb_error_t* error);
 /* split merged keys into slots (u64), distances (f32) and counts (i64) -- all device pointers */
 RB_EXPORT void rb_unpack_topk_device(void const* d_keys, uint64_t query_count, uint32_t k, void* d_slots_out,
                                      void* d_distances_out, void* d_counts_out, uintptr_t stream, rb_error_t* error);

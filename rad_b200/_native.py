@@ -90,6 +90,9 @@ SIGNATURES = {
     "rb_dedup_workspace_bytes": (C.c_size_t, [C.c_uint64]),
     "rb_dedup_device": (None, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, _ERR]),
     "rb_popcounts_device": (None, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t, _ERR]),
+    "rb_sharded_search_workspace_bytes": (C.c_size_t, [C.c_size_t, C.c_size_t, C.c_uint32]),
+    "rb_sharded_search_device": (None, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_size_t,
+                                        C.c_void_p, C.c_void_p, C.c_size_t, _ERR]),
     "rb_cluster_device": (None, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_void_p, _ERR]),
     "rb_stable_match_workspace_bytes": (C.c_size_t, [C.c_uint64, C.c_uint64]),
     "rb_stable_match_device": (None, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint32, C.c_void_p,

@@ -17,6 +17,8 @@
 #include <thread>
 #include <vector>
 
+#include <dlfcn.h>
+
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
@@ -1989,6 +1991,145 @@ void rb_merge_topk_device(void const* d_partial_keys, uint32_t parts, uint64_t q
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess)
         RB_FAIL(std::string("CUDA error in merge: ") + cudaGetErrorString(e));
+}
+
+// ---------------------------------------------------------------------------------------------- sharded search over NCCL
+// The exchange of a multi-GPU search behind the C ABI (no host framework needed): NCCL is reached through dlopen at the
+// first call -- the copy already loaded in the process if there is one (e.g. PyTorch's), else libnccl.so.2 from the
+// loader's path -- so the library has no link-time dependency on it and single-GPU users never load it.
+namespace {
+struct NcclApi {
+    // ncclResult_t ncclAllGather(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) etc. (nccl.h)
+    int (*all_gather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*comm_count)(void*, int*) = nullptr;
+    const char* (*error_string)(int) = nullptr;
+    std::string problem;
+};
+constexpr int kNcclUint64 = 5;  // ncclDataType_t: ncclUint64 (nccl.h)
+
+NcclApi const& nccl_api() {
+    static NcclApi api = [] {
+        NcclApi a;
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+        if (!h)
+            h = dlopen("libnccl.so.2", RTLD_NOW);
+        if (!h) {
+            a.problem = std::string("libnccl.so.2 cannot be loaded: ") + dlerror();
+            return a;
+        }
+        a.all_gather = reinterpret_cast<decltype(a.all_gather)>(dlsym(h, "ncclAllGather"));
+        a.comm_count = reinterpret_cast<decltype(a.comm_count)>(dlsym(h, "ncclCommCount"));
+        a.error_string = reinterpret_cast<decltype(a.error_string)>(dlsym(h, "ncclGetErrorString"));
+        if (!a.all_gather || !a.comm_count || !a.error_string)
+            a.problem = "libnccl.so.2 lacks ncclAllGather / ncclCommCount / ncclGetErrorString";
+        return a;
+    }();
+    return api;
+}
+
+struct ShardedSearchLayout {
+    size_t slots, dists, counts, local_keys, gathered, total;
+};
+ShardedSearchLayout sharded_search_layout(size_t nq, size_t k, uint32_t world) {
+    ShardedSearchLayout L{};
+    auto take = [&](size_t bytes) {
+        size_t at = L.total;
+        L.total += (bytes + 255) & ~(size_t)255;
+        return at;
+    };
+    L.slots = take(nq * k * 4), L.dists = take(nq * k * 4), L.counts = take(nq * 4);
+    L.local_keys = take(nq * k * 8), L.gathered = take((size_t)world * nq * k * 8);
+    return L;
+}
+
+// (slot, distance, count) answers of one shard -> merge keys in GLOBAL slots (distance bits << 32 | ~slot; ~0 = none)
+__global__ void pack_topk_kernel(const uint32_t* slots, const float* dists, const int32_t* counts, uint64_t query_count,
+                                 uint32_t k, uint64_t slot_base, uint64_t* keys) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= query_count * k)
+        return;
+    const uint64_t q = i / k;
+    const uint32_t j = (uint32_t)(i % k);
+    keys[i] = (int32_t)j < counts[q]
+                  ? ((uint64_t)__float_as_uint(dists[i]) << 32) | (uint32_t)~(uint32_t)(slot_base + slots[i])
+                  : ~0ull;
+}
+
+std::string sharded_search(rb_index* ix, uint64_t slot_base, void const* d_queries, size_t nq, size_t k, bool exact,
+                           void* comm, uint64_t* d_keys_out, void* d_workspace, size_t workspace_bytes) {
+    NcclApi const& nccl = nccl_api();
+    if (!nccl.problem.empty())
+        return nccl.problem;
+    int world = 0;
+    int rc = nccl.comm_count(comm, &world);
+    if (rc != 0)
+        return std::string("ncclCommCount: ") + nccl.error_string(rc);
+    if (slot_base + ix->host.size() > (1ull << 32))
+        return "sharded search addresses at most 2^32 global slots";
+    const ShardedSearchLayout L = sharded_search_layout(nq, k, (uint32_t)world);
+    if (workspace_bytes < L.total)
+        return "workspace smaller than rb_sharded_search_workspace_bytes(query_count, k, world)";
+    std::string err = ensure_device(ix);
+    if (!err.empty())
+        return err;
+    DeviceState& d = ix->dev;
+    uint8_t* ws = static_cast<uint8_t*>(d_workspace);
+    uint32_t* slots = reinterpret_cast<uint32_t*>(ws + L.slots);
+    float* dists = reinterpret_cast<float*>(ws + L.dists);
+    int32_t* counts = reinterpret_cast<int32_t*>(ws + L.counts);
+    uint64_t* local_keys = reinterpret_cast<uint64_t*>(ws + L.local_keys);
+    uint64_t* gathered = reinterpret_cast<uint64_t*>(ws + L.gathered);
+    if (ix->host.size()) {  // an empty shard answers with no candidates
+        if (!(err = prepare_search(ix, k)).empty())
+            return err;
+        size_t x_bytes = exact ? exact_scratch_bytes(ix->host.size(), nq, k) : 0;
+        if (!(err = ensure_scratch(d, x_bytes)).empty())
+            return err;
+        err = search_on_device(ix, static_cast<uint4 const*>(d_queries), nq, k, exact, slots, dists, counts, d.scratch,
+                               x_bytes);
+        if (!err.empty())
+            return err;
+    } else {
+        RB_CUDA(cudaMemsetAsync(counts, 0, nq * 4, d.stream));
+    }
+    pack_topk_kernel<<<(unsigned)((nq * k + 255) / 256), 256, 0, d.stream>>>(slots, dists, counts, nq, (uint32_t)k,
+                                                                             slot_base, local_keys);
+    RB_CUDA(cudaGetLastError());
+    rc = nccl.all_gather(local_keys, gathered, nq * k, kNcclUint64, comm, d.stream);
+    if (rc != 0)
+        return std::string("ncclAllGather: ") + nccl.error_string(rc);
+    rb::MergeParams mp;
+    mp.partial_keys = gathered;
+    mp.parts = (uint32_t)world;
+    mp.query_count = (uint32_t)nq;
+    mp.k = (uint32_t)k;
+    mp.keys_out = d_keys_out;
+    rb::merge_topk_kernel<<<(unsigned)((nq + 3) / 4), 128, 4 * k * 8, d.stream>>>(mp);
+    RB_CUDA(cudaGetLastError());
+    RB_CUDA(cudaStreamSynchronize(d.stream));
+    ix->last.kernel_launches += 2;
+    return {};
+}
+}  // namespace
+
+size_t rb_sharded_search_workspace_bytes(size_t query_count, size_t k, uint32_t world) {
+    return sharded_search_layout(query_count, k, world ? world : 1).total;
+}
+
+void rb_sharded_search_device(rb_index_t* ix, uint64_t slot_base, void const* d_queries, size_t query_count, size_t k,
+                              int exact, uintptr_t nccl_comm, void* d_keys_out, void* d_workspace,
+                              size_t workspace_bytes, rb_error_t* error) {
+    if (error)
+        *error = nullptr;
+    if (!query_count)
+        return;
+    if (!k || k > 1024)
+        RB_FAIL("k must be in 1..1024");
+    std::string err = sharded_search(ix, slot_base, d_queries, query_count, k, exact != 0,
+                                     reinterpret_cast<void*>(nccl_comm), static_cast<uint64_t*>(d_keys_out),
+                                     d_workspace, workspace_bytes);
+    if (!err.empty())
+        RB_FAIL(err);
 }
 
 // ---------------------------------------------------------------------------------------------- ingest: duplicates
