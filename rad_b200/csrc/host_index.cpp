@@ -457,6 +457,7 @@ int64_t HostIndex::check_new_keys(uint64_t const* new_keys, size_t n) {
     }
     if (ascending)
         return -1;
+    std::lock_guard<std::mutex> lock(mu_);  // may run beside readers (and on the add's helper thread)
     if (!map_valid_)
         rebuild_keymap();
     KeyMap fresh;
