@@ -525,7 +525,7 @@ def _stitch_rows(shard, slot_base: int, comm, batch: int, kr: int, efm: int):
     return rows_global, sizes
 
 
-def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 65536,
+def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 262144,
                        k_remote: int | None = None, ef_merge: int | None = None, timings: dict | None = None,
                        comm=None, assemble: bool = True, gather_below: int = 262144, rebuild_upper: bool = False):
     """ONE HNSW graph with global slots from the sub-graphs every rank built over its own row shard (SURVEY.md §8e
