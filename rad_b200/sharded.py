@@ -525,7 +525,14 @@ def _stitch_rows(shard, slot_base: int, comm, batch: int, kr: int, efm: int):
     return rows_global, sizes
 
 
-def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int = 262144,
+def stitch_round_size(world: int, k_remote: int) -> int:
+    """Nodes per rank and round of the stitch.  The graph does not depend on it; larger rounds mean fewer launch tails
+    and synchronisations (262 144 instead of 65 536: 9 % less stitch time at two shards).  The candidate exchange of a
+    round is world x round x k_remote x 128 bytes per rank and is kept to 1 GiB, the largest measured."""
+    return 262144 if world * k_remote * 128 * 262144 <= (1 << 30) else 65536
+
+
+def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch: int | None = None,
                        k_remote: int | None = None, ef_merge: int | None = None, timings: dict | None = None,
                        comm=None, assemble: bool = True, gather_below: int = 262144, rebuild_upper: bool = False):
     """ONE HNSW graph with global slots from the sub-graphs every rank built over its own row shard (SURVEY.md §8e
@@ -557,6 +564,8 @@ def build_global_graph(shard, slot_base: int, *, expansion_add: int = 128, batch
     dev = shard.device
     kr, efm = stitch_parameters(world)
     kr, efm = k_remote or kr, ef_merge or efm
+    if batch is None:
+        batch = stitch_round_size(world, kr)
     n_local, m = len(shard), shard.m
     t_start = time.perf_counter()
 
